@@ -1,0 +1,137 @@
+/*
+ * fpemu_b200.h — C ABI of libfpemu_b200.so, the B200 (sm_100a) replacement for the native side of
+ * the FP8-Emulation-Toolkit `fpemu_cuda` operator.
+ *
+ * Every entry point takes plain pointers and sizes (no torch types), enqueues work on the stream the
+ * caller passes (a cudaStream_t as void*; NULL = legacy default stream), never synchronises the device
+ * and, unless stated otherwise, never allocates or frees device memory.
+ *
+ * Return convention (replaces the reference's `fprintf(stderr) + exit(1)`,
+ * mpemu/pytquant/cuda/fpemu_kernels.cu:1037-1041, and AT_CUDA_CHECK throws, :1071):
+ *      0  success
+ *     <0  invalid argument (FPEMU_ERR_*)
+ *     >0  a cudaError_t raised by the launch
+ * fpemu_strerror() turns any of them into text.
+ */
+#ifndef FPEMU_B200_H
+#define FPEMU_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Target number formats.  Reference kernels: fpemu_kernels.cu E5M2_Kernel :375-463, E5M2_DAZ_Kernel
+ * :465-541 (format E5M2 + FPEMU_FLAG_DAZ), E4M3_Kernel :543-654, E3M4_Kernel :873-984,
+ * BFLOAT16_Kernel :243-305, FLOAT16_Kernel :307-373, E4M3_IEEE_Kernel :656-767,
+ * FP4_Nearest_Kernel :986-1024. */
+enum {
+  FPEMU_FMT_E5M2 = 0,
+  FPEMU_FMT_E4M3 = 1,
+  FPEMU_FMT_E3M4 = 2,
+  FPEMU_FMT_BF16 = 3,
+  FPEMU_FMT_FP16 = 4,
+  FPEMU_FMT_E4M3_IEEE = 5,
+  FPEMU_FMT_FP4 = 6,
+  FPEMU_FMT_COUNT = 7
+};
+
+/* Rounding modes; numeric values equal the reference's ROUNDING_MODES (fpemu_kernels.cu:17-18). */
+enum {
+  FPEMU_RND_RTZ = 0,        /* truncate                                  */
+  FPEMU_RND_RNE = 1,        /* nearest, ties to even                     */
+  FPEMU_RND_STOCHASTIC = 2, /* P(round away) = dropped fraction          */
+  FPEMU_RND_RNAZ = 3,       /* nearest, ties away from zero              */
+  FPEMU_RND_RNTZ = 4,       /* nearest, ties toward zero                 */
+  FPEMU_RND_RPINF = 5,      /* reference "round to +INF" (sic: >= half)  */
+  FPEMU_RND_RNINF = 6,      /* reference "round to -INF" (sic: >= half)  */
+  FPEMU_RND_COUNT = 7
+};
+
+/* Flags. */
+enum {
+  FPEMU_FLAG_DAZ = 1,          /* denormal flush variants: E5M2_DAZ_*, FLOAT16_DAZ_RNE               */
+  FPEMU_FLAG_UNSCALE_FP32 = 2  /* multiply by 1/scale in fp32 like the reference CPU op
+                                  (cpp/fpemu_impl.cpp:761,1131,1716).  Default (flag clear) rounds the
+                                  un-scaled value through fp16 like the reference CUDA op
+                                  (fpemu_kernels.cu:461,539,652,982).                                 */
+};
+
+/* Element types of the in/out buffers (both buffers always share one type). */
+enum { FPEMU_DT_F32 = 0, FPEMU_DT_F16 = 1, FPEMU_DT_BF16 = 2, FPEMU_DT_COUNT = 3 };
+
+/* Error codes. */
+enum {
+  FPEMU_OK = 0,
+  FPEMU_ERR_MODE = -1,     /* unknown mode string / format / rounding combination */
+  FPEMU_ERR_DTYPE = -2,    /* unsupported element type                            */
+  FPEMU_ERR_SCALE = -3,    /* scale > 65504 (reference: exit(1))                  */
+  FPEMU_ERR_ARG = -4,      /* null pointer, negative size, bad block size, ...    */
+  FPEMU_ERR_ALIGN = -5,    /* pointer not aligned to its element size             */
+  FPEMU_ERR_TOO_LARGE = -6 /* problem exceeds a documented fixed capacity         */
+};
+
+/* Library version (major*10000 + minor*100 + patch). */
+int fpemu_version(void);
+
+/* Text for a status returned by any entry point (static storage, never NULL). */
+const char* fpemu_strerror(int status);
+
+/* Parse a reference mode string ("E4M3_RNE", "E5M2_DAZ_STOCHASTIC", "BFLOAT16_RNE", ...) into
+ * (format, rounding, flags).  Replaces the `mode.compare(...)` chain of fpemu_cuda_forward,
+ * fpemu_kernels.cu:1058-1364.  Besides the reference's strings it accepts <FMT>_RTZ for E4M3, E3M4,
+ * BFLOAT16 (truncate = "same pipeline, rounding add 0").  Unknown strings return
+ * FPEMU_ERR_MODE (the reference silently returns zeros, :1375-1380). */
+int fpemu_parse_mode(const char* mode, int* format, int* rounding, int* flags);
+
+/* Elementwise quantize-dequantize cast of n elements: out[i] = QDQ(in[i]).  in == out is allowed
+ * (in-place).  Replaces the kernel launches of fpemu_cuda_forward (fpemu_kernels.cu:1028-1381) for
+ * block_norm == false.
+ *   scale    host scalar applied before rounding; the result is multiplied by 1/scale.
+ *   d_scale  optional DEVICE pointer to one float; when non-NULL it overrides `scale` (no host sync;
+ *            fed by fpemu_scale_from_amax).
+ *   seed, elem_offset  stochastic rounding uses Philox4x32-10 keyed by seed with the counter derived
+ *            from (elem_offset + i), so a tensor cast in slabs gives the same bits as in one piece.
+ */
+int fpemu_cast(const void* in, void* out, int64_t n, int dtype, int format, int rounding, int flags,
+               float scale, const float* d_scale, uint64_t seed, uint64_t elem_offset, void* stream);
+
+/* Blocked cast ("block_norm"): every run of block_size consecutive elements gets its own power-of-two
+ * scale derived from its absolute maximum, 2*2^floor(log2 max)/K with K = 16384 (E5M2), 8 (E4M3,
+ * E4M3_IEEE), 1 (E3M4); FP4 uses 1/max.  Replaces absmax_block + the per-kernel scale derivation,
+ * fpemu_kernels.cu:150-170, :407-414, :575-582, :905-912.  n must be a multiple of block_size
+ * (the reference silently disables blocking otherwise, :1048-1051; this ABI returns FPEMU_ERR_ARG and
+ * leaves that policy to the caller). */
+int fpemu_cast_blocked(const void* in, void* out, int64_t n, int64_t block_size, int dtype, int format,
+                       int rounding, int flags, uint64_t seed, uint64_t elem_offset, void* stream);
+
+/* Single-pass absolute maximum of n elements, max-accumulated into *d_amax (device float the caller
+ * initialised, normally to 0; NaN inputs are ignored like torch.max on |x| never is — see DESIGN.md).
+ * Replaces `torch.max(torch.abs(tensor.flatten()))` of mpemu/qutils.py:282. */
+int fpemu_amax(const void* in, int64_t n, int dtype, float* d_amax, void* stream);
+
+/* d_scale[i] = clamp(flt_max / d_amax[i]) for i < count, with the reference's clamp
+ * `scale = 6.55e4 if scale > 3.275e4` (mpemu/qutils.py:283-285).  Device-side, no host sync. */
+int fpemu_scale_from_amax(const float* d_amax, int count, float flt_max, float* d_scale, void* stream);
+
+/* Row-wise (per-channel) amax-scaled cast of a rows x cols row-major matrix: each row gets
+ * scale = clamp(flt_max / max|row|).  One launch replaces the Python per-channel loop of
+ * mpemu/qutils.py:289-311.  d_row_scale (optional, rows floats) receives the scales used. */
+int fpemu_cast_rowwise(const void* in, void* out, int64_t rows, int64_t cols, int dtype, int format,
+                       int rounding, int flags, float flt_max, float* d_row_scale, uint64_t seed,
+                       uint64_t elem_offset, void* stream);
+
+/* Host-buffer convenience used by the end-to-end measurement: casts n elements that live in HOST
+ * memory (pinned for full speed) into a HOST output, staging through two caller-provided device
+ * buffers of chunk_elems elements each (d_stage[0], d_stage[1]) so the H2D copy, the kernel and the
+ * D2H copy of consecutive chunks overlap on the three streams given.  Synchronises the three streams
+ * before returning. */
+int fpemu_cast_host(const void* h_in, void* h_out, int64_t n, int dtype, int format, int rounding,
+                    int flags, float scale, uint64_t seed, void* d_stage0, void* d_stage1,
+                    int64_t chunk_elems, void* stream_h2d, void* stream_compute, void* stream_d2h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FPEMU_B200_H */
