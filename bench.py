@@ -1,0 +1,350 @@
+#!/usr/bin/env python
+"""bench.py — fpemu cast throughput on B200 (BASELINE.json metric: cast GB/s & % of HBM peak).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--elems E] [--impl ours|reference]
+
+A *step* is one pass of the hot path over one batch of synthetic input: the format x rounding sweep of
+BASELINE.json configs[1] — {E5M2, E4M3, E3M4, BFLOAT16} x {RNE, STOCHASTIC, RTZ} out-of-place QDQ casts of one
+2^30-element fp32 tensor per GPU (scale 1), plus one per-tensor amax-scaled E4M3_RNE cast (amax kernel ->
+[NCCL all-reduce MAX of one float when N > 1] -> device-side scale -> cast).  Each rank owns
+its own 2^30-element row slab (weak scaling); the only communication is that 4-byte all-reduce.
+
+value = algorithmic bytes of all ranks / max-over-ranks device time (8 B/elem per plain cast: read 1 + write 1
+fp32; 12 B/elem for the amax-scaled cast: amax read + cast read + write).  Inputs (4 GiB per tensor) are far
+larger than the 126 MB L2, so no explicit flush is needed between iterations.
+
+`--impl reference` times the reference's own CPU op (oracle/_ref, built unmodified from
+/root/reference/mpemu/pytquant/cpp/fpemu_impl.cpp) on the host cores on a bounded sample of the same sweep.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+PKG = os.path.join(ROOT, "fp8-emulation-toolkit_b200")
+for p in (ROOT, PKG):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+FORMATS = ["E5M2", "E4M3", "E3M4", "BFLOAT16"]
+ROUNDINGS = ["RNE", "STOCHASTIC", "RTZ"]
+SWEEP = ["%s_%s" % (f, r) for f in FORMATS for r in ROUNDINGS]
+# the reference's dispatcher has no truncate mode for E4M3 / E3M4 / BFLOAT16 (fpemu_impl.cpp:1866-2009)
+REF_SWEEP = [m for m in SWEEP if not (m.endswith("_RTZ") and not m.startswith("E5M2"))]
+METRIC = "fpemu_cast_throughput"
+UNIT = "GB/s"
+
+
+def measured_peak():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def committed_traffic(kernel_key):
+    """dram__bytes_read+write per launch of the dominant kernel from the committed ncu --set full capture."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "roofline_traffic.json")) as f:
+            return json.load(f).get(kernel_key)
+    except Exception:
+        return None
+
+
+class ClockSampler(object):
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.proc = None
+        self.path = None
+
+    def start(self):
+        try:
+            fd, self.path = tempfile.mkstemp(suffix=".csv")
+            os.close(fd)
+            self.f = open(self.path, "w")
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "200"], stdout=self.f,
+                                         stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        if self.proc is None:
+            return out
+        try:
+            self.proc.terminate()
+            self.proc.wait(timeout=5)
+            self.f.close()
+            sm, mx, reasons = [], [], set()
+            names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+            with open(self.path) as f:
+                for line in f:
+                    p = [c.strip() for c in line.split(",")]
+                    if len(p) < 7:
+                        continue
+                    try:
+                        sm.append(float(p[0])); mx.append(float(p[1]))
+                    except ValueError:
+                        continue
+                    for nm, val in zip(names, p[3:7]):
+                        if val.lower().startswith("active"):
+                            reasons.add(nm)
+            os.unlink(self.path)
+            if sm:
+                out = {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons),
+                       "samples": len(sm)}
+        except Exception:
+            pass
+        return out
+
+
+# ---------------------------------------------------------------------------------------------- reference arm
+def time_reference_cpu(n_elems, steps, warmup, modes):
+    """Seconds per sweep of the reference CPU op over `modes` on an n_elems fp32 tensor, all host threads."""
+    import torch
+    from oracle import ref_loader
+    mod, label = ref_loader.best_cpu()
+    if mod is None:
+        return None, label, 0
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    g = torch.Generator().manual_seed(0)
+    x = torch.randn(n_elems, dtype=torch.float32, generator=g)
+
+    def sweep():
+        for m in modes:
+            mod.forward(x, m, n_elems, False, 1.0, False, 1)
+    for _ in range(warmup):
+        sweep()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        sweep()
+    dt = (time.perf_counter() - t0) / steps
+    return dt, label, cores
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    n = args.ref_elems
+    dt, label, cores = time_reference_cpu(n, args.steps, args.warmup, REF_SWEEP)
+    if dt is None:
+        print(json.dumps({"impl": "reference", "unavailable": label}))
+        return 0
+    gbs = 8.0 * n * len(REF_SWEEP) / dt / 1e9
+    sample = ("reference CPU op (%s build of mpemu/pytquant/cpp/fpemu_impl.cpp), %d-mode sweep (%s) of one 2^%d-element "
+              "fp32 tensor per step, host memory only" % (label, len(REF_SWEEP), ",".join(REF_SWEEP), n.bit_length() - 1))
+    line = {"impl": "reference", "metric": METRIC, "value": gbs, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "format x rounding QDQ sweep, fp32, scale 1 (BASELINE configs[1]); CPU sample size 2^%d elements"
+                                   % (n.bit_length() - 1), "modes": REF_SWEEP},
+            "cpu_baseline": {"value": gbs, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample},
+            "e2e": {"value": gbs, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+    return 0
+
+
+# ---------------------------------------------------------------------------------------------- our arm
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    import fpemu_b200 as F
+    import fpemu_cuda
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    F._lib.lib()                                                   # fail loudly if the CUDA library is missing
+
+    n = args.elems
+    g = torch.Generator(device=dev).manual_seed(1234 + rank)
+    x = torch.randn(n, dtype=torch.float32, device=dev, generator=g)
+    y = torch.empty_like(x)
+    d_amax = torch.zeros(1, dtype=torch.float32, device=dev)
+    slab_offset = rank * n                                         # this rank's row slab of the world x n tensor
+
+    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(len(SWEEP) + 2)] for _ in range(args.steps)]
+
+    def step(k=None):
+        for i, mode in enumerate(SWEEP):
+            if k is not None:
+                ev[k][i].record()
+            fpemu_cuda_forward_raw(F, x, y, mode, seed=1000 + i, elem_offset=slab_offset)
+        if k is not None:
+            ev[k][len(SWEEP)].record()
+        # per-tensor amax-scaled E4M3 cast, global amax over all slabs
+        d_amax.zero_()
+        F.amax(x, out=d_amax)
+        if world > 1:
+            dist.all_reduce(d_amax, op=dist.ReduceOp.MAX)
+        F.cast_amax_scaled(x, "E4M3_RNE", out=y, d_amax=d_amax)
+        if k is not None:
+            ev[k][len(SWEEP) + 1].record()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier()
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    t_start = torch.cuda.Event(enable_timing=True)
+    t_stop = torch.cuda.Event(enable_timing=True)
+    t_start.record()
+    for k in range(args.steps):
+        step(k)
+    t_stop.record()
+    barrier()
+    clk = clocks.stop() if rank == 0 else None
+    elapsed_ms = t_start.elapsed_time(t_stop)
+    t = torch.tensor([elapsed_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    elapsed_ms = float(t.item())
+
+    bytes_per_step_rank = 8.0 * n * len(SWEEP) + 12.0 * n
+    value = bytes_per_step_rank * world * args.steps / (elapsed_ms * 1e-3) / 1e9
+
+    # per-launch durations (device events inside the timed region, this rank)
+    per_mode = {}
+    for i, mode in enumerate(SWEEP):
+        ms = [ev[k][i].elapsed_time(ev[k][i + 1]) for k in range(args.steps)]
+        per_mode[mode] = sum(ms) / len(ms)
+    amax_scaled_ms = sum(ev[k][len(SWEEP)].elapsed_time(ev[k][len(SWEEP) + 1]) for k in range(args.steps)) / args.steps
+
+    # ---- end to end: host buffers in, host buffers out, copies inside the timed region
+    e2e = None
+    if not args.no_e2e:
+        ne = min(args.e2e_elems, n)
+        h_in = torch.randn(ne, dtype=torch.float32).pin_memory()
+        h_out = torch.empty(ne, dtype=torch.float32).pin_memory()
+        caster = F.HostCaster(torch.float32, chunk_elems=1 << 24, device=local)
+        xd = torch.empty(ne, dtype=torch.float32, device=dev)
+
+        def e2e_step():
+            for i, mode in enumerate(SWEEP):
+                caster.run(h_in, h_out, mode, seed=1000 + i)
+            xd.copy_(h_in, non_blocking=True)
+            d_amax.zero_()
+            F.amax(xd, out=d_amax)
+            if world > 1:
+                dist.all_reduce(d_amax, op=dist.ReduceOp.MAX)
+            F.cast_amax_scaled(xd, "E4M3_RNE", out=xd, d_amax=d_amax)
+            h_out.copy_(xd, non_blocking=True)
+            torch.cuda.synchronize()
+        e2e_step()
+        barrier()
+        e2e_steps = max(1, min(args.steps, args.e2e_steps))
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            e2e_step()
+        barrier()
+        dt = time.perf_counter() - t0
+        tt = torch.tensor([dt], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        dt = float(tt.item())
+        e2e_bytes = (8.0 * ne * len(SWEEP) + 12.0 * ne) * world * e2e_steps
+        e2e = {"value": e2e_bytes / dt / 1e9, "unit": UNIT,
+               "h2d_bytes_per_step": int(4 * ne * (len(SWEEP) + 1)), "d2h_bytes_per_step": int(4 * ne * (len(SWEEP) + 1)),
+               "elems_per_tensor": ne, "steps": e2e_steps,
+               "api": "fpemu_cast_host (C ABI, pinned host in/out, 2 x 64 MiB device staging, 3 streams)"}
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+
+    peak, peak_src = measured_peak()
+    dominant = max(per_mode, key=lambda m: per_mode[m])
+    dom_ms = per_mode[dominant]
+    achieved = 8.0 * n / (dom_ms * 1e-3) / 1e9
+    detail = {m: {"ms": round(per_mode[m], 4), "GB/s": round(8.0 * n / (per_mode[m] * 1e-3) / 1e9, 1),
+                  "frac_of_peak": round(8.0 * n / (per_mode[m] * 1e-3) / 1e9 / peak, 4)} for m in SWEEP}
+    detail["E4M3_RNE_amax_scaled"] = {"ms": round(amax_scaled_ms, 4),
+                                      "GB/s": round(12.0 * n / (amax_scaled_ms * 1e-3) / 1e9, 1),
+                                      "frac_of_peak": round(12.0 * n / (amax_scaled_ms * 1e-3) / 1e9 / peak, 4)}
+
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "format x rounding QDQ sweep {E5M2,E4M3,E3M4,BFLOAT16}x{RNE,STOCHASTIC,RTZ} + amax-scaled "
+                                   "E4M3_RNE on one 2^%d-element fp32 tensor per GPU, out-of-place (BASELINE configs[1])"
+                                   % (n.bit_length() - 1),
+                       "elems_per_gpu": n, "modes": SWEEP + ["E4M3_RNE_amax_scaled"],
+                       "l2": "inputs (%.1f GiB per tensor) larger than L2, no flush" % (4.0 * n / 2 ** 30),
+                       "parallelism": "row slabs, one rank per GPU, one 4-byte NCCL all-reduce(MAX) per step"},
+            "roofline": {"bound": "hbm", "kernel": "cast_vec_kernel<%s>" % dominant, "achieved": achieved, "peak": peak,
+                         "unit": "GB/s", "frac": achieved / peak, "traffic": committed_traffic(dominant),
+                         "peak_source": peak_src, "algorithmic_bytes_per_launch": 8 * n,
+                         "avg_launch_ms": dom_ms, "frac_of_nominal_8000": achieved / 8000.0},
+            "detail": detail,
+            "clocks": clk,
+            "gpu_launches": args.steps * (len(SWEEP) + 3)}
+    if e2e is not None:
+        line["e2e"] = e2e
+
+    if world == 1 and not args.no_cpu:
+        dt, label, cores = time_reference_cpu(args.ref_elems, 3, 1, REF_SWEEP)
+        if dt is not None:
+            line["cpu_baseline"] = {
+                "value": 8.0 * args.ref_elems * len(REF_SWEEP) / dt / 1e9, "unit": UNIT, "cores": cores, "kind": "reference",
+                "sample": "reference CPU op (%s build), %d-mode sweep of one 2^%d-element fp32 tensor, 3 timed passes"
+                          % (label, len(REF_SWEEP), args.ref_elems.bit_length() - 1)}
+        else:
+            line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": label}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def fpemu_cuda_forward_raw(F, x, y, mode, seed, elem_offset):
+    """One cast launch through the C ABI into a preallocated output (the plugin boundary `fpemu_cuda.forward`
+    allocates its result like the reference does; the device-resident measurement excludes the allocator)."""
+    F.cast(x, mode, out=y, seed=seed, elem_offset=elem_offset)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--elems", type=int, default=1 << 30, help="elements per GPU per tensor")
+    ap.add_argument("--e2e-elems", type=int, default=1 << 28)
+    ap.add_argument("--e2e-steps", type=int, default=2)
+    ap.add_argument("--ref-elems", type=int, default=1 << 24, help="CPU sample size (reference arm / cpu_baseline)")
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_ours(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,185 @@
+// fpemu_cast.cu — the elementwise quantize-dequantize cast (C ABI: fpemu_cast).
+//
+// Replaces the kernel launches of the reference's fpemu_cuda_forward
+// (mpemu/pytquant/cuda/fpemu_kernels.cu:1028-1381) for block_norm == false.
+//
+// Data movement: one 256-bit LDG + one 256-bit STG per thread per vector (8 fp32 / 16 half elements),
+// kUnroll vectors in flight per thread, warp-contiguous (thread t of a CTA touches vector base + t), grid
+// sized to a multiple of the SM count with a grid-stride loop.  No shared memory, no scratch memory.
+// Algorithmic traffic: read 1 + write 1 element = 8 B/elem (fp32) or 4 B/elem (fp16 / bf16).
+#include "fpemu_cast_core.cuh"
+
+namespace fpemu {
+
+template <int FMT, int RND, bool DAZ, int DT, bool SCALED>
+__global__ void __launch_bounds__(kThreads) cast_vec_kernel(const CastArgs a) {
+  constexpr int VE = DtInfo<DT>::kVecElems;
+  ScaleCtx sc;
+  sc.scale = 1.0f; sc.rscale = 1.0f;
+  sc.unscale32 = (a.flags & FPEMU_FLAG_UNSCALE_FP32) != 0;
+  if (SCALED) {
+    float s = a.d_scale ? __ldg(a.d_scale) : a.scale;
+    s = effective_scale(s, DT);
+    sc.scale = s;
+    sc.rscale = __frcp_rn(s);                 // == (float)(1.0 / (double)s): `float r = 1.0 / scale;`
+  }
+  const int64_t nvec = a.n / VE;
+  const char* in = static_cast<const char*>(a.in);
+  char* out = static_cast<char*>(a.out);
+  const int64_t stride = (int64_t)gridDim.x * (kThreads * kUnroll);
+  for (int64_t base = (int64_t)blockIdx.x * (kThreads * kUnroll) + threadIdx.x; base < nvec; base += stride) {
+    Vec32 v[kUnroll];
+#pragma unroll
+    for (int j = 0; j < kUnroll; ++j) {
+      const int64_t vi = base + j * kThreads;
+      if (vi < nvec) v[j] = ldg256(in + vi * 32);
+    }
+#pragma unroll
+    for (int j = 0; j < kUnroll; ++j) {
+      const int64_t vi = base + j * kThreads;
+      if (vi < nvec) {
+        process_vec<FMT, RND, DAZ, DT, SCALED>(v[j], sc, a, a.elem_offset + (uint64_t)vi * VE);
+        stg256(out + vi * 32, v[j]);
+      }
+    }
+  }
+  // ragged tail (< one vector): staged through a zero-padded register vector so it runs the same code
+  const int tail = (int)(a.n - nvec * VE);
+  if (tail > 0 && blockIdx.x == gridDim.x - 1 && threadIdx.x == 0) {
+    Vec32 v;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) v.w[i] = 0u;
+    const int64_t e0 = nvec * VE;
+    if (DT == FPEMU_DT_F32) {
+      const uint32_t* p = reinterpret_cast<const uint32_t*>(a.in) + e0;
+      for (int i = 0; i < tail; ++i) v.w[i] = p[i];
+    } else {
+      const unsigned short* p = reinterpret_cast<const unsigned short*>(a.in) + e0;
+      for (int i = 0; i < tail; ++i) v.w[i >> 1] |= (uint32_t)p[i] << ((i & 1) * 16);
+    }
+    process_vec<FMT, RND, DAZ, DT, SCALED>(v, sc, a, a.elem_offset + (uint64_t)e0);
+    if (DT == FPEMU_DT_F32) {
+      uint32_t* p = reinterpret_cast<uint32_t*>(a.out) + e0;
+      for (int i = 0; i < tail; ++i) p[i] = v.w[i];
+    } else {
+      unsigned short* p = reinterpret_cast<unsigned short*>(a.out) + e0;
+      for (int i = 0; i < tail; ++i) p[i] = (unsigned short)(v.w[i >> 1] >> ((i & 1) * 16));
+    }
+  }
+}
+
+// Every format x rounding mode, any alignment, per-element random draws.  Correctness path, not the fast one.
+__global__ void __launch_bounds__(256) cast_generic_kernel(const CastArgs a, const int dt) {
+  const bool scaled = (a.d_scale != nullptr) || (a.scale != 1.0f);
+  float s = 1.0f, rs = 1.0f;
+  if (scaled) {
+    s = effective_scale(a.d_scale ? __ldg(a.d_scale) : a.scale, dt);
+    rs = __frcp_rn(s);
+  }
+  const bool wide = (a.fmt == FPEMU_FMT_BF16 || a.fmt == FPEMU_FMT_FP16);
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < a.n; i += stride) {
+    const float x = load_elem(a.in, i, dt);
+    uint32_t rb = 0u;
+    if (a.rnd == FPEMU_RND_STOCHASTIC) rb = rand_bits_one(a.seed_lo, a.seed_hi, a.elem_offset + (uint64_t)i, wide);
+    store_elem(a.out, i, dt, cast_one(x, a.fmt, a.rnd, a.flags, scaled, s, rs, dt == FPEMU_DT_F16, rb));
+  }
+}
+
+// ------------------------------------------------------------------------------------------ dispatch
+typedef void (*CastKernel)(const CastArgs);
+
+template <int FMT, int RND, bool DAZ, int DT>
+static CastKernel pick_scaled(bool scaled) {
+  if (FMT == FPEMU_FMT_BF16 || FMT == FPEMU_FMT_FP16) return cast_vec_kernel<FMT, RND, DAZ, DT, false>;
+  return scaled ? cast_vec_kernel<FMT, RND, DAZ, DT, true> : cast_vec_kernel<FMT, RND, DAZ, DT, false>;
+}
+
+template <int FMT, int RND, bool DAZ>
+static CastKernel pick_dt(int dt, bool scaled) {
+  switch (dt) {
+    case FPEMU_DT_F32:  return pick_scaled<FMT, RND, DAZ, FPEMU_DT_F32>(scaled);
+    case FPEMU_DT_F16:  return pick_scaled<FMT, RND, DAZ, FPEMU_DT_F16>(scaled);
+    default:            return pick_scaled<FMT, RND, DAZ, FPEMU_DT_BF16>(scaled);
+  }
+}
+
+template <int FMT>
+static CastKernel pick_rnd(int rnd, bool daz, int dt, bool scaled) {
+  if (FMT == FPEMU_FMT_E5M2 && daz) {
+    if (rnd == FPEMU_RND_RNE) return pick_dt<FPEMU_FMT_E5M2, FPEMU_RND_RNE, true>(dt, scaled);
+    if (rnd == FPEMU_RND_STOCHASTIC) return pick_dt<FPEMU_FMT_E5M2, FPEMU_RND_STOCHASTIC, true>(dt, scaled);
+    return nullptr;
+  }
+  switch (rnd) {
+    case FPEMU_RND_RNE:        return pick_dt<FMT, FPEMU_RND_RNE, false>(dt, scaled);
+    case FPEMU_RND_RTZ:        return (FMT == FPEMU_FMT_FP16) ? nullptr : pick_dt<FMT, FPEMU_RND_RTZ, false>(dt, scaled);
+    case FPEMU_RND_STOCHASTIC: return pick_dt<FMT, FPEMU_RND_STOCHASTIC, false>(dt, scaled);
+    default:                   return nullptr;
+  }
+}
+
+static CastKernel pick_kernel(int fmt, int rnd, bool daz, int dt, bool scaled) {
+  switch (fmt) {
+    case FPEMU_FMT_E5M2: return pick_rnd<FPEMU_FMT_E5M2>(rnd, daz, dt, scaled);
+    case FPEMU_FMT_E4M3: return pick_rnd<FPEMU_FMT_E4M3>(rnd, daz, dt, scaled);
+    case FPEMU_FMT_E3M4: return pick_rnd<FPEMU_FMT_E3M4>(rnd, daz, dt, scaled);
+    case FPEMU_FMT_BF16: return pick_rnd<FPEMU_FMT_BF16>(rnd, false, dt, false);
+    case FPEMU_FMT_FP16: return pick_rnd<FPEMU_FMT_FP16>(rnd, false, dt, false);
+    default:             return nullptr;   // E4M3_IEEE, FP4: generic kernel
+  }
+}
+
+int validate_cast(int64_t n, int dtype, int format, int rounding, float scale, const void* in, const void* out) {
+  if (n < 0) return FPEMU_ERR_ARG;
+  if (dtype < 0 || dtype >= FPEMU_DT_COUNT) return FPEMU_ERR_DTYPE;
+  if (format < 0 || format >= FPEMU_FMT_COUNT || rounding < 0 || rounding >= FPEMU_RND_COUNT) return FPEMU_ERR_MODE;
+  if (format == FPEMU_FMT_FP16 && rounding != FPEMU_RND_RNE && rounding != FPEMU_RND_STOCHASTIC) return FPEMU_ERR_MODE;
+  if (!(scale <= 65504.0f)) return FPEMU_ERR_SCALE;             // also rejects NaN
+  if (n > 0 && (in == nullptr || out == nullptr)) return FPEMU_ERR_ARG;
+  const uintptr_t esz = (uintptr_t)dtype_bytes(dtype);
+  if (((uintptr_t)in % esz) || ((uintptr_t)out % esz)) return FPEMU_ERR_ALIGN;
+  return FPEMU_OK;
+}
+
+int launch_cast(const CastArgs& a, int dtype, cudaStream_t stream) {
+  if (a.n == 0) return FPEMU_OK;
+  const bool scaled = (a.d_scale != nullptr) || (a.scale != 1.0f);
+  const bool daz = (a.flags & FPEMU_FLAG_DAZ) != 0;
+  const bool aligned = (((uintptr_t)a.in | (uintptr_t)a.out) & 31u) == 0;
+  const bool rng_ok = (a.rnd != FPEMU_RND_STOCHASTIC) || ((a.elem_offset & 15u) == 0);
+  CastKernel k = (aligned && rng_ok) ? pick_kernel(a.fmt, a.rnd, daz, dtype, scaled) : nullptr;
+  const int sms = device_info().sm_count;
+  if (k != nullptr) {
+    const int ve = dtype == FPEMU_DT_F32 ? 8 : 16;
+    const int64_t nvec = a.n / ve;
+    const int64_t per_cta = (int64_t)kThreads * kUnroll;
+    int64_t want = (nvec + per_cta - 1) / per_cta;
+    if (want < 1) want = 1;
+    const int64_t cap = (int64_t)sms * FPEMU_CAST_CTAS_PER_SM;
+    const int grid = (int)(want < cap ? want : cap);
+    k<<<grid, kThreads, 0, stream>>>(a);
+  } else {
+    int64_t want = (a.n + 255) / 256;
+    const int64_t cap = (int64_t)sms * 8;
+    const int grid = (int)(want < cap ? want : cap);
+    cast_generic_kernel<<<grid, 256, 0, stream>>>(a, dtype);
+  }
+  return (int)cudaGetLastError();
+}
+
+}  // namespace fpemu
+
+extern "C" int fpemu_cast(const void* in, void* out, int64_t n, int dtype, int format, int rounding, int flags,
+                          float scale, const float* d_scale, uint64_t seed, uint64_t elem_offset, void* stream) {
+  int st = fpemu::validate_cast(n, dtype, format, rounding, d_scale ? 1.0f : scale, in, out);
+  if (st != FPEMU_OK) return st;
+  fpemu::CastArgs a;
+  a.in = in; a.out = out; a.n = n;
+  a.scale = scale; a.d_scale = d_scale;
+  a.seed_lo = (uint32_t)seed; a.seed_hi = (uint32_t)(seed >> 32);
+  a.elem_offset = elem_offset;
+  a.fmt = format; a.rnd = rounding; a.flags = flags;
+  if (format == FPEMU_FMT_BF16 || format == FPEMU_FMT_FP16) { a.scale = 1.0f; a.d_scale = nullptr; }  // no scale in these kernels
+  return fpemu::launch_cast(a, dtype, static_cast<cudaStream_t>(stream));
+}

@@ -1,0 +1,116 @@
+// fpemu_cast_core.cuh — per-vector body of the cast, shared by the plain, blocked and row-wise kernels.
+#pragma once
+
+#include "fpemu_common.cuh"
+
+namespace fpemu {
+
+struct CastArgs {
+  const void* in;
+  void* out;
+  int64_t n;
+  float scale;
+  const float* d_scale;
+  uint32_t seed_lo, seed_hi;
+  uint64_t elem_offset;
+  int fmt, rnd, flags;
+};
+
+constexpr int kThreads = 256;
+#ifndef FPEMU_CAST_UNROLL
+#define FPEMU_CAST_UNROLL 2
+#endif
+constexpr int kUnroll = FPEMU_CAST_UNROLL;
+#ifndef FPEMU_CAST_CTAS_PER_SM
+#define FPEMU_CAST_CTAS_PER_SM 8
+#endif
+
+struct ScaleCtx { float scale, rscale; bool unscale32; };
+
+template <int DT>
+__device__ __forceinline__ float2 get_pair(const Vec32& v, int k) {
+  if (DT == FPEMU_DT_F32) return make_float2(__uint_as_float(v.w[2 * k]), __uint_as_float(v.w[2 * k + 1]));
+  if (DT == FPEMU_DT_F16) return unpack_f16x2(v.w[k]);
+  return unpack_bf16x2(v.w[k]);
+}
+template <int DT>
+__device__ __forceinline__ void put_pair(Vec32& v, int k, float2 f) {
+  if (DT == FPEMU_DT_F32) { v.w[2 * k] = __float_as_uint(f.x); v.w[2 * k + 1] = __float_as_uint(f.y); }
+  else if (DT == FPEMU_DT_F16) v.w[k] = pack_f16x2_rn(f.x, f.y);
+  else v.w[k] = pack_bf16x2_rn(f.x, f.y);
+}
+
+// One 32-byte vector whose first element has global index g0 (a multiple of the vector length).
+template <int FMT, int RND, bool DAZ, int DT, bool SCALED>
+__device__ __forceinline__ void process_vec(Vec32& v, const ScaleCtx& sc, const CastArgs& a, uint64_t g0) {
+  constexpr int kPairs = DtInfo<DT>::kVecElems / 2;
+  constexpr bool kSR = (RND == FPEMU_RND_STOCHASTIC);
+
+  if (FMT == FPEMU_FMT_E5M2 || FMT == FPEMU_FMT_E4M3 || FMT == FPEMU_FMT_E3M4) {
+    // random bytes: element g uses byte (g % 16) of Philox(g / 16)
+    uint32_t rw[4] = {0u, 0u, 0u, 0u};
+    if (kSR) {
+      const uint4 r = philox4x32_10(a.seed_lo, a.seed_hi, g0 >> 4);
+      const uint32_t m = (FMT == FPEMU_FMT_E5M2) ? 0xFFFFFFFFu : (FMT == FPEMU_FMT_E4M3 ? 0x7F7F7F7Fu : 0x3F3F3F3Fu);
+      if (DT == FPEMU_DT_F32) {                       // 8 elements: half of the 16-byte draw
+        const bool hi = (g0 >> 3) & 1u;
+        rw[0] = (hi ? r.z : r.x) & m; rw[1] = (hi ? r.w : r.y) & m;
+      } else {
+        rw[0] = r.x & m; rw[1] = r.y & m; rw[2] = r.z & m; rw[3] = r.w & m;
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < kPairs; ++k) {
+      uint32_t h;
+      if (DT == FPEMU_DT_F16 && !SCALED) {
+        h = v.w[k];
+      } else {
+        float2 f = get_pair<DT>(v, k);
+        if (SCALED) { f.x *= sc.scale; f.y *= sc.scale; }
+        h = pack_f16x2_rn(f.x, f.y);
+      }
+      const uint32_t r2 = kSR ? __byte_perm(rw[k >> 1], 0u, (k & 1) ? 0x4342u : 0x4140u) : 0u;
+      uint32_t q = round_pair<FMT, RND, DAZ>(h, r2);
+      if (DT == FPEMU_DT_F16) {
+        if (SCALED) {
+          float2 g = unpack_f16x2(q);
+          q = pack_f16x2_rn(g.x * sc.rscale, g.y * sc.rscale);
+        }
+        v.w[k] = q;
+      } else {
+        float2 g = unpack_f16x2(q);
+        if (SCALED) {
+          g.x *= sc.rscale; g.y *= sc.rscale;
+          if (!sc.unscale32) g = unpack_f16x2(pack_f16x2_rn(g.x, g.y));   // reference CUDA op: through fp16
+        }
+        put_pair<DT>(v, k, g);
+      }
+    }
+  } else {
+    // BFLOAT16 / FLOAT16 targets: per element on fp32 bits; 16 random bits per element,
+    // element g uses 16-bit lane (g % 8) of Philox(g / 8)
+    const bool daz = (a.flags & FPEMU_FLAG_DAZ) != 0;
+#pragma unroll
+    for (int k = 0; k < kPairs; ++k) {
+      uint32_t rbits = 0u;
+      if (kSR) {
+        // pair k covers elements 2k, 2k+1 -> Philox call (2k / 8), lanes (2k % 8), (2k % 8) + 1 = one word
+        const uint4 r = philox4x32_10(a.seed_lo, a.seed_hi, (g0 >> 3) + (uint64_t)((2 * k) >> 3));
+        const int wsel = ((2 * k) & 7) >> 1;
+        rbits = wsel == 0 ? r.x : (wsel == 1 ? r.y : (wsel == 2 ? r.z : r.w));
+      }
+      float2 f = get_pair<DT>(v, k);
+      if (FMT == FPEMU_FMT_BF16) {
+        f.x = __uint_as_float(round_one_bf16(__float_as_uint(f.x), RND, rbits & 0xFFFFu));
+        f.y = __uint_as_float(round_one_bf16(__float_as_uint(f.y), RND, rbits >> 16));
+      } else {
+        const bool ih = (DT == FPEMU_DT_F16);
+        f.x = __half2float(__ushort_as_half((unsigned short)round_one_fp16(f.x, RND, daz, ih, rbits & 0xFFFFu)));
+        f.y = __half2float(__ushort_as_half((unsigned short)round_one_fp16(f.y, RND, daz, ih, rbits >> 16)));
+      }
+      put_pair<DT>(v, k, f);
+    }
+  }
+}
+
+}  // namespace fpemu

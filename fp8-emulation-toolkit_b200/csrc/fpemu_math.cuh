@@ -1,0 +1,272 @@
+// fpemu_math.cuh — register-level arithmetic of the B200 fpemu cast.
+//
+// Two implementations of the same rounding rules live here and are tested against each other and
+// against the CPU restatement used by the tests:
+//   * round_pair_*  : two fp16 values packed in one 32-bit register, branch-free, built from LOP3 /
+//                     IADD3 / HSET2 / HMNMX2 so that one warp instruction serves 64 elements.  These are
+//                     the hot path (RNE / RTZ / stochastic for E5M2, E5M2_DAZ, E4M3, E3M4).
+//   * round_one     : one element, every format and rounding mode of the reference's mode grammar.
+//                     Used for tails, unaligned buffers and the rarely used modes.
+//
+// Semantics follow the reference CUDA kernels (mpemu/pytquant/cuda/fpemu_kernels.cu): fp32 -> fp16 with
+// round-to-nearest-even first, then integer rounding of the fp16 encoding:
+//   E5M2      :375-463   keep 2 mantissa bits; carry may reach Inf; NaN/Inf only masked
+//   E5M2_DAZ  :465-541   same, fp16 subnormals (and zeros) become +0
+//   E4M3      :543-654   |h| >= 448 (Inf, NaN too) -> +-448; |h| < 2^-9 -> +-0; for 2^-9 <= |h| < 2^-6 the
+//                        low (9 - e) bits are cleared first, i.e. |h| is truncated to a multiple of 2^-16
+//   E3M4      :873-984   |h| >= 30 -> +-30; |h| < 2^-6 -> +-0; |h| truncated to a multiple of 2^-12
+//   BFLOAT16  :243-305   on fp32 bits; exponent field 0 -> +0
+//   FLOAT16   :307-373
+//   E4M3_IEEE :656-767, FP4 :986-1024
+#pragma once
+
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <stdint.h>
+
+#include "../../include/fpemu_b200.h"
+
+namespace fpemu {
+
+// ------------------------------------------------------------------------------------------ bit casts
+__device__ __forceinline__ __half2 as_h2(uint32_t u) { return *reinterpret_cast<__half2*>(&u); }
+__device__ __forceinline__ uint32_t as_u32(__half2 h) { return *reinterpret_cast<uint32_t*>(&h); }
+__device__ __forceinline__ uint32_t as_u32(__nv_bfloat162 h) { return *reinterpret_cast<uint32_t*>(&h); }
+
+__device__ __forceinline__ uint32_t pack_f16x2_rn(float lo, float hi) { return as_u32(__floats2half2_rn(lo, hi)); }
+__device__ __forceinline__ uint32_t pack_bf16x2_rn(float lo, float hi) { return as_u32(__floats2bfloat162_rn(lo, hi)); }
+__device__ __forceinline__ float2 unpack_f16x2(uint32_t h2) { return __half22float2(as_h2(h2)); }
+__device__ __forceinline__ float2 unpack_bf16x2(uint32_t b2) {
+  return make_float2(__uint_as_float(b2 << 16), __uint_as_float(b2 & 0xFFFF0000u));
+}
+
+// ------------------------------------------------------------------------------------------ Philox4x32-10
+// Counter-based generator (Salmon et al., SC'11).  key = 64-bit seed, counter = (ctr, 0, 0).
+struct PhiloxKeys { uint32_t k0[10], k1[10]; };
+
+__device__ __forceinline__ uint4 philox4x32_10(uint32_t seed_lo, uint32_t seed_hi, uint64_t ctr) {
+  uint32_t c0 = (uint32_t)ctr, c1 = (uint32_t)(ctr >> 32), c2 = 0u, c3 = 0u;
+  uint32_t k0 = seed_lo, k1 = seed_hi;
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    uint64_t p0 = (uint64_t)0xD2511F53u * c0;
+    uint64_t p1 = (uint64_t)0xCD9E8D57u * c2;
+    uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ k0;
+    uint32_t n2 = (uint32_t)(p0 >> 32) ^ c3 ^ k1;
+    c1 = (uint32_t)p1; c3 = (uint32_t)p0; c0 = n0; c2 = n2;
+    k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+  }
+  return make_uint4(c0, c1, c2, c3);
+}
+
+// Random bits of ONE element with global index g (slow path; the vector path draws 16 / 8 elements per call).
+// 8-bit formats: byte (g % 16) of Philox(g / 16);  BF16 / FP16: 16-bit lane (g % 8) of Philox(g / 8).
+__device__ __forceinline__ uint32_t rand_bits_one(uint32_t seed_lo, uint32_t seed_hi, uint64_t g, bool wide) {
+  uint4 w = philox4x32_10(seed_lo, seed_hi, wide ? (g >> 3) : (g >> 4));
+  uint32_t words[4] = {w.x, w.y, w.z, w.w};
+  if (wide) {
+    uint32_t lane = (uint32_t)g & 7u;
+    return (words[lane >> 1] >> ((lane & 1u) * 16u)) & 0xFFFFu;
+  }
+  uint32_t lane = (uint32_t)g & 15u;
+  return (words[lane >> 2] >> ((lane & 3u) * 8u)) & 0xFFu;
+}
+
+// ------------------------------------------------------------------------------------------ packed pairs
+// All functions take/return two fp16 encodings in one register.  `r2` carries the random bits of the
+// two lanes in bits [0,8) and [16,24) (already masked to the format's dropped-bit count).
+
+constexpr uint32_t kAbs2 = 0x7FFF7FFFu;
+constexpr uint32_t kSign2 = 0x80008000u;
+
+__device__ __forceinline__ uint32_t h2c(uint16_t bits) { return (uint32_t)bits | ((uint32_t)bits << 16); }
+
+template <int RND, bool DAZ>
+__device__ __forceinline__ uint32_t round_pair_e5m2(uint32_t h, uint32_t r2) {
+  constexpr uint32_t kKeep = 0xFF00FF00u;
+  const __half2 hv = as_h2(h);
+  const __half2 av = as_h2(h & kAbs2);
+  const __half2 min_normal = as_h2(h2c(0x0400));
+  if (RND == FPEMU_RND_RTZ && !DAZ) return h & kKeep;
+  if (!DAZ) {
+    if (RND == FPEMU_RND_RNE) {
+      // h + 0x7F + lsb, NaN lanes untouched (Inf + 0x7F stays Inf after the mask)
+      uint32_t ok = __heq2_mask(hv, hv);
+      uint32_t lsb = (h >> 8) & 0x00010001u & ok;
+      return (h + (0x007F007Fu & ok) + lsb) & kKeep;
+    }
+    // stochastic: fp16-normal lanes add 8 random bits, fp16-subnormal lanes round to nearest even
+    uint32_t is_sub = __hlt2_mask(av, min_normal);
+    uint32_t is_nrm = __hlt2_mask(av, as_h2(h2c(0x7C00))) & ~is_sub;
+    uint32_t rne = 0x007F007Fu + ((h >> 8) & 0x00010001u);
+    uint32_t inc = (r2 & is_nrm) | (rne & is_sub);
+    return (h + inc) & kKeep;
+  }
+  // DAZ: only fp16-normal lanes are rounded; exponent-field-0 lanes (zeros included) become +0
+  uint32_t is_sub = __hlt2_mask(av, min_normal);            // false for NaN: NaN lanes are only masked
+  uint32_t is_nrm = __hge2_mask(av, min_normal);            // true for Inf: harmless, low bits are 0
+  uint32_t inc;
+  if (RND == FPEMU_RND_RNE) inc = (0x007F007Fu + ((h >> 8) & 0x00010001u)) & is_nrm;
+  else if (RND == FPEMU_RND_STOCHASTIC) inc = r2 & is_nrm & __hlt2_mask(av, as_h2(h2c(0x7C00)));
+  else inc = 0u;
+  return (h + inc) & kKeep & ~is_sub;
+}
+
+// E4M3 (LSHIFT 7, SAT 0x5F00 = 448, FLUSH 0x1800 = 2^-9, grid exponents 9 -> thresholds 2^-6, 2^-7, 2^-8) and
+// E3M4 (LSHIFT 6, SAT 0x4F80 = 30,  FLUSH 0x2400 = 2^-6, thresholds 2^-2 .. 2^-5) share one shape.
+template <int FMT, int RND>
+__device__ __forceinline__ uint32_t round_pair_e4m3_like(uint32_t h, uint32_t r2) {
+  constexpr bool E4 = (FMT == FPEMU_FMT_E4M3);
+  constexpr uint32_t kSat = E4 ? 0x5F005F00u : 0x4F804F80u;
+  constexpr uint32_t kFlush = E4 ? 0x18001800u : 0x24002400u;
+  constexpr uint32_t kKeep = E4 ? 0xFF80FF80u : 0xFFC0FFC0u;
+  constexpr uint32_t kHalfM1 = E4 ? 0x003F003Fu : 0x001F001Fu;
+  constexpr int kL = E4 ? 7 : 6;
+  const uint32_t sign = h & kSign2;
+  // saturate: min(|h|, max) as fp16 numbers; NaN and Inf lanes become max (min returns the non-NaN operand)
+  uint32_t a = as_u32(__hmin2(as_h2(h & kAbs2), as_h2(kSat)));
+  const __half2 av = as_h2(a);
+  const uint32_t keep = __hge2_mask(av, as_h2(kFlush));     // lanes below the flush threshold -> signed zero
+  uint32_t r;
+  if (RND == FPEMU_RND_RTZ) {
+    r = a & kKeep;                                          // clearing <= 4 low bits first changes nothing
+  } else {
+    // truncate |h| to a multiple of 2^-16 (E4M3) / 2^-12 (E3M4): clear 1..3 (1..4) low bits by binade
+    uint32_t m;
+    if (E4) {
+      uint32_t l9 = __hlt2_mask(av, as_h2(h2c(0x2400)));    // < 2^-6 : clear >= 1 bit
+      uint32_t l8 = __hlt2_mask(av, as_h2(h2c(0x2000)));    // < 2^-7 : clear >= 2 bits
+      uint32_t l7 = __hlt2_mask(av, as_h2(h2c(0x1C00)));    // < 2^-8 : clear 3 bits
+      m = l9 & (0x00010001u | (l8 & (0x00020002u | (l7 & 0x00040004u))));
+    } else {
+      uint32_t l13 = __hlt2_mask(av, as_h2(h2c(0x3400)));   // < 2^-2
+      uint32_t l12 = __hlt2_mask(av, as_h2(h2c(0x3000)));   // < 2^-3
+      uint32_t l11 = __hlt2_mask(av, as_h2(h2c(0x2C00)));   // < 2^-4
+      uint32_t l10 = __hlt2_mask(av, as_h2(h2c(0x2800)));   // < 2^-5
+      m = l13 & (0x00010001u | (l12 & (0x00020002u | (l11 & (0x00040004u | (l10 & 0x00080008u))))));
+    }
+    uint32_t ac = a & ~m;
+    uint32_t inc = (RND == FPEMU_RND_RNE) ? (kHalfM1 + ((ac >> kL) & 0x00010001u)) : r2;
+    r = (ac + inc) & kKeep;                                 // a saturated lane has zero low bits: unchanged
+  }
+  return sign | (r & keep);
+}
+
+template <int FMT, int RND, bool DAZ>
+__device__ __forceinline__ uint32_t round_pair(uint32_t h, uint32_t r2) {
+  if (FMT == FPEMU_FMT_E5M2) return round_pair_e5m2<RND, DAZ>(h, r2);
+  return round_pair_e4m3_like<FMT, RND>(h, r2);
+}
+
+// ------------------------------------------------------------------------------------------ one element
+// Rounding increment decision shared by every format: `v` is the integer whose low L bits get dropped.
+__device__ __forceinline__ uint32_t round_up_bit(uint32_t v, int L, int rnd, bool pos, bool neg) {
+  const uint32_t grs = v & ((1u << L) - 1u);
+  const uint32_t half = 1u << (L - 1);
+  switch (rnd) {
+    case FPEMU_RND_RNE:   return (grs > half) || (grs == half && ((v >> L) & 1u));
+    case FPEMU_RND_RNAZ:  return grs >= half;
+    case FPEMU_RND_RNTZ:  return grs > half;
+    case FPEMU_RND_RPINF: return pos && grs >= half;
+    case FPEMU_RND_RNINF: return neg && grs >= half;
+    default:              return 0u;
+  }
+}
+
+// fp16 encoding -> rounded fp16 encoding, formats E5M2 / E4M3 / E3M4 / E4M3_IEEE.
+__device__ __forceinline__ uint32_t round_one_h16(uint32_t h, int fmt, int rnd, bool daz, uint32_t rbits) {
+  const uint32_t a = h & 0x7FFFu, sign = h & 0x8000u;
+  const bool pos = (sign == 0u) && a != 0u && a <= 0x7C00u;   // `h.f > 0` (false for NaN)
+  const bool neg = (sign != 0u) && a != 0u && a <= 0x7C00u;
+  if (fmt == FPEMU_FMT_E5M2) {
+    if (a >= 0x7C00u) return h & 0xFF00u;
+    if (a < 0x0400u) {
+      if (daz) return 0u;
+      const int r = (rnd == FPEMU_RND_STOCHASTIC) ? FPEMU_RND_RNE : rnd;
+      return (h + (round_up_bit(h, 8, r, pos, neg) << 8)) & 0xFF00u;
+    }
+    const uint32_t inc = (rnd == FPEMU_RND_STOCHASTIC) ? (rbits & 0xFFu) : (round_up_bit(h, 8, rnd, pos, neg) << 8);
+    return (h + inc) & 0xFF00u;
+  }
+  int L, grid_e;
+  uint32_t sat, sat_out, flush, round_below;
+  if (fmt == FPEMU_FMT_E3M4) { L = 6; sat = 0x4F80u; sat_out = 0x4F80u; flush = 0x2400u; grid_e = 13; round_below = sat; }
+  else if (fmt == FPEMU_FMT_E4M3) { L = 7; sat = 0x5F00u; sat_out = 0x5F00u; flush = 0x1800u; grid_e = 9; round_below = sat; }
+  else { L = 7; sat = 0x5C00u; sat_out = 0x7C00u; flush = 0x1800u; grid_e = 9; round_below = 0x4B80u; }  // E4M3_IEEE
+  if (a >= sat) return sign | sat_out;
+  if (a < flush) return sign;
+  const int d = grid_e - (int)(a >> 10);
+  const uint32_t ac = (d > 0) ? (a & ~((1u << d) - 1u)) : a;
+  uint32_t inc = 0u;
+  if (a < round_below)
+    inc = (rnd == FPEMU_RND_STOCHASTIC) ? (rbits & ((1u << L) - 1u)) : (round_up_bit(ac, L, rnd, pos, neg) << L);
+  return sign | ((ac + inc) & ~((1u << L) - 1u));
+}
+
+// BFLOAT16 on fp32 bits (fpemu_kernels.cu:266-304).
+__device__ __forceinline__ uint32_t round_one_bf16(uint32_t u, int rnd, uint32_t rbits) {
+  const uint32_t e = u & 0x7F800000u;
+  if (e == 0u) return 0u;                                       // zeros and denormals -> +0
+  if (e != 0x7F800000u) {
+    if (rnd == FPEMU_RND_STOCHASTIC) u += rbits & 0xFFFFu;
+    else if (rnd == FPEMU_RND_RNE || rnd == FPEMU_RND_RNAZ || rnd == FPEMU_RND_RNTZ)
+      u += round_up_bit(u, 16, rnd, false, false) << 16;
+  }
+  return u & 0xFFFF0000u;
+}
+
+// FLOAT16 (fpemu_kernels.cu:318-372): returns the fp16 encoding.
+__device__ __forceinline__ uint32_t round_one_fp16(float x, int rnd, bool daz, bool input_is_half, uint32_t rbits) {
+  if (input_is_half || rnd != FPEMU_RND_STOCHASTIC) {
+    uint32_t h = __half_as_ushort(__float2half_rn(x));
+    if (daz && (h & 0x7C00u) == 0u) h = 0u;
+    return h;
+  }
+  const uint32_t u = __float_as_uint(x);
+  const int e = (int)((u >> 23) & 0xFFu) - 127;
+  const uint32_t sign16 = (u >> 16) & 0x8000u;
+  uint32_t m = u & 0x7FFFFFu;
+  if (e == 128) {                                               // Inf / NaN (signalling NaNs get quieted)
+    if (m != 0u) m |= 0x400000u;
+    return sign16 | 0x7C00u | (m >> 13);
+  }
+  if (e >= 16) return sign16 | 0x7C00u;
+  if (e < -14) return __half_as_ushort(__float2half_rn(x));     // fp16 subnormal range: plain RNE
+  m = (m | ((uint32_t)(e + 15) << 23)) + (rbits & 0x1FFFu);     // 13 random bits, carry may bump the exponent
+  return (sign16 | (m >> 13)) & 0xFFFFu;
+}
+
+// FP4 "nearest" on an fp32 value (fpemu_kernels.cu:1002-1023): powers of 4, 1.6x round-up trick.
+__device__ __forceinline__ float round_one_fp4(float v) {
+  uint32_t u = __float_as_uint(v);
+  int e = (int)((u >> 23) & 0xFFu) - 127;
+  const uint32_t sign = u & 0x80000000u;
+  if (e < 0 && (e % 2)) u = __float_as_uint((float)((double)v * 1.6));
+  if (e > 0) u = sign | (127u << 23);
+  u &= 0xFF800000u;
+  e = (int)((u >> 23) & 0xFFu) - 127;
+  if (e < 0 && (e % 2)) u = sign | ((uint32_t)(e + 126) << 23);
+  if (e < -12) u = 0u;
+  return __uint_as_float(u);
+}
+
+// Full QDQ of one fp32 value (already widened from the tensor's dtype).  `scale`/`rscale` are what the
+// kernel uses (for fp16 tensors the scale has been rounded to half, see cast kernels).
+__device__ __forceinline__ float cast_one(float x, int fmt, int rnd, int flags, bool scaled, float scale,
+                                          float rscale, bool input_is_half, uint32_t rbits) {
+  const bool daz = (flags & FPEMU_FLAG_DAZ) != 0;
+  if (fmt == FPEMU_FMT_BF16) return __uint_as_float(round_one_bf16(__float_as_uint(x), rnd, rbits));
+  if (fmt == FPEMU_FMT_FP16)
+    return __half2float(__ushort_as_half((unsigned short)round_one_fp16(x, rnd, daz, input_is_half, rbits)));
+  if (fmt == FPEMU_FMT_FP4) return round_one_fp4(scaled ? scale * x : x) * (scaled ? rscale : 1.0f);
+  const uint32_t h = __half_as_ushort(__float2half_rn(scaled ? x * scale : x));
+  const uint32_t q = round_one_h16(h, fmt, rnd, daz, rbits);
+  float f = __half2float(__ushort_as_half((unsigned short)q));
+  if (scaled) {
+    f = f * rscale;
+    if (!(flags & FPEMU_FLAG_UNSCALE_FP32)) f = __half2float(__float2half_rn(f));
+  }
+  return f;
+}
+
+}  // namespace fpemu

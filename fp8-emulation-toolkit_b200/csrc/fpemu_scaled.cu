@@ -1,0 +1,391 @@
+// fpemu_scaled.cu — everything that derives a scale from the data before casting:
+//   fpemu_amax             single-pass |x| maximum (vector loads -> warp redux -> one atomicMax per CTA)
+//   fpemu_scale_from_amax  device-side `flt_max / amax` + clamp of mpemu/qutils.py:283-285
+//   fpemu_cast_blocked     per-block power-of-two scale ("block_norm", fpemu_kernels.cu:150-170 + :407-414 ...)
+//   fpemu_cast_rowwise     per-channel amax-scaled cast (replaces the Python loop of mpemu/qutils.py:289-311)
+#include "fpemu_cast_core.cuh"
+
+namespace fpemu {
+
+// ------------------------------------------------------------------------------------------ amax
+// max |x| of one 32-byte vector as a non-negative float; NaN lanes are ignored (fmaxf / hmax2 semantics,
+// as the reference's absmax0, fpemu_kernels.cu:194-195).
+template <int DT>
+__device__ __forceinline__ float vec_absmax(const Vec32& v) {
+  if (DT == FPEMU_DT_F32) {
+    float m = 0.0f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) m = fmaxf(m, fabsf(__uint_as_float(v.w[i])));
+    return m;
+  } else if (DT == FPEMU_DT_F16) {
+    __half2 m = as_h2(0u);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) m = __hmax2(m, as_h2(v.w[i] & kAbs2));
+    return fmaxf(__low2float(m), __high2float(m));
+  } else {
+    uint32_t z = 0u;
+    __nv_bfloat162 m = *reinterpret_cast<__nv_bfloat162*>(&z);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      uint32_t a = v.w[i] & kAbs2;
+      m = __hmax2(m, *reinterpret_cast<__nv_bfloat162*>(&a));
+    }
+    return fmaxf(__low2float(m), __high2float(m));
+  }
+}
+
+constexpr int kAmaxThreads = 256;
+constexpr int kAmaxUnroll = 4;
+
+template <int DT>
+__global__ void __launch_bounds__(kAmaxThreads) amax_kernel(const void* in_, int64_t n, float* d_amax) {
+  constexpr int VE = DtInfo<DT>::kVecElems;
+  const char* in = static_cast<const char*>(in_);
+  const int64_t nvec = n / VE;
+  float m = 0.0f;
+  const int64_t stride = (int64_t)gridDim.x * (kAmaxThreads * kAmaxUnroll);
+  for (int64_t base = (int64_t)blockIdx.x * (kAmaxThreads * kAmaxUnroll) + threadIdx.x; base < nvec; base += stride) {
+    Vec32 v[kAmaxUnroll];
+#pragma unroll
+    for (int j = 0; j < kAmaxUnroll; ++j) {
+      const int64_t vi = base + j * kAmaxThreads;
+      if (vi < nvec) v[j] = ldg256(in + vi * 32);
+      else {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) v[j].w[i] = 0u;
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < kAmaxUnroll; ++j) m = fmaxf(m, vec_absmax<DT>(v[j]));
+  }
+  // ragged tail
+  if (blockIdx.x == 0 && threadIdx.x < (int)(n - nvec * VE))
+    m = fmaxf(m, fabsf(load_elem(in_, nvec * VE + threadIdx.x, DT)));
+  uint32_t bits = warp_max_u32(__float_as_uint(m));
+  __shared__ uint32_t warp_bits[kAmaxThreads / 32];
+  if ((threadIdx.x & 31) == 0) warp_bits[threadIdx.x >> 5] = bits;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    bits = threadIdx.x < kAmaxThreads / 32 ? warp_bits[threadIdx.x] : 0u;
+    bits = warp_max_u32(bits);
+    if (threadIdx.x == 0 && bits != 0u) atomicMax(reinterpret_cast<unsigned int*>(d_amax), bits);
+  }
+}
+
+// unaligned buffers: scalar loads
+__global__ void __launch_bounds__(256) amax_generic_kernel(const void* in, int64_t n, int dt, float* d_amax) {
+  float m = 0.0f;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+    m = fmaxf(m, fabsf(load_elem(in, i, dt)));
+  uint32_t bits = warp_max_u32(__float_as_uint(m));
+  if ((threadIdx.x & 31) == 0 && bits != 0u) atomicMax(reinterpret_cast<unsigned int*>(d_amax), bits);
+}
+
+__device__ __forceinline__ float scale_from_amax(float amax, float flt_max, bool clamp) {
+  float s = __fdiv_rn(flt_max, amax);                       // `scale = flt_max / vmax`
+  if (clamp && s > 3.275e4f) s = 6.55e4f;                   // `scale = 6.55e+04 if scale > 3.275e+04`
+  return s;
+}
+
+__global__ void scale_from_amax_kernel(const float* d_amax, int count, float flt_max, float* d_scale) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < count) d_scale[i] = scale_from_amax(d_amax[i], flt_max, true);
+}
+
+// ------------------------------------------------------------------------------------------ blocked
+// Power-of-two block scale from the block maximum (fpemu_kernels.cu:409-413, 577-581, 909-911, 998).
+__device__ __forceinline__ float block_scale(float maxval, int fmt, int dt) {
+  const float p2 = __uint_as_float(__float_as_uint(maxval) & 0x7F800000u);
+  switch (fmt) {
+    case FPEMU_FMT_E5M2:
+      if (dt == FPEMU_DT_F16) {                              // `scalar_t scale` is a half in this instantiation
+        float s = __half2float(__float2half_rn(2.0f * p2));
+        return __half2float(__float2half_rn(s * (1.0f / 16384.0f)));
+      }
+      return (2.0f * p2) * (1.0f / 16384.0f);
+    case FPEMU_FMT_E4M3:
+    case FPEMU_FMT_E4M3_IEEE: return (2.0f * p2) * 0.125f;
+    case FPEMU_FMT_E3M4:      return 2.0f * p2;
+    default:                  return __fdiv_rn(1.0f, maxval);    // FP4: 1 / max
+  }
+}
+
+// Fast path: a quantization block is `vpb` (power of two, <= 32) consecutive 32-byte vectors, i.e. it lives in
+// `vpb` adjacent lanes of one warp: xor-shuffle butterfly, everything stays in registers (8 B/elem fp32).
+template <int FMT, int RND, int DT>
+__global__ void __launch_bounds__(kThreads) blocked_vec_kernel(const CastArgs a, const int vpb) {
+  constexpr int VE = DtInfo<DT>::kVecElems;
+  const int64_t nvec = a.n / VE;                            // n % block_size == 0 and block_size % VE == 0
+  const char* in = static_cast<const char*>(a.in);
+  char* out = static_cast<char*>(a.out);
+  ScaleCtx sc;
+  sc.unscale32 = (a.flags & FPEMU_FLAG_UNSCALE_FP32) != 0;
+  const int64_t stride = (int64_t)gridDim.x * kThreads;
+  // every lane of a warp runs the same number of iterations (shuffles need the full warp)
+  const int64_t nvec_pad = (nvec + 31) & ~(int64_t)31;
+  for (int64_t vi = (int64_t)blockIdx.x * kThreads + threadIdx.x; vi < nvec_pad; vi += stride) {
+    const bool live = vi < nvec;
+    Vec32 v;
+    if (live) v = ldg256(in + vi * 32);
+    else {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) v.w[i] = 0u;
+    }
+    uint32_t mb = __float_as_uint(vec_absmax<DT>(v));
+    for (int d = 1; d < vpb; d <<= 1) mb = max(mb, __shfl_xor_sync(0xFFFFFFFFu, mb, d));
+    const float s = block_scale(__uint_as_float(mb), FMT, DT);
+    sc.scale = s;
+    sc.rscale = __frcp_rn(s);
+    if (live) {
+      process_vec<FMT, RND, false, DT, true>(v, sc, a, a.elem_offset + (uint64_t)vi * VE);
+      stg256(out + vi * 32, v);
+    }
+  }
+}
+
+// General path: one warp per quantization block of any size / alignment / format; two passes over the block
+// (the second one is served by L1/L2).
+__global__ void __launch_bounds__(256) blocked_generic_kernel(const CastArgs a, const int64_t block_size, const int dt) {
+  const int lane = threadIdx.x & 31;
+  const int64_t nblocks = a.n / block_size;
+  const int64_t warp0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  const bool wide = (a.fmt == FPEMU_FMT_BF16 || a.fmt == FPEMU_FMT_FP16);
+  for (int64_t b = warp0; b < nblocks; b += nwarps) {
+    const int64_t e0 = b * block_size;
+    float m = 0.0f;
+    for (int64_t i = lane; i < block_size; i += 32) m = fmaxf(m, fabsf(load_elem(a.in, e0 + i, dt)));
+    m = __uint_as_float(warp_max_u32(__float_as_uint(m)));
+    const float s = block_scale(m, a.fmt, dt);
+    const float rs = __frcp_rn(s);
+    for (int64_t i = lane; i < block_size; i += 32) {
+      const float x = load_elem(a.in, e0 + i, dt);
+      uint32_t rb = 0u;
+      if (a.rnd == FPEMU_RND_STOCHASTIC) rb = rand_bits_one(a.seed_lo, a.seed_hi, a.elem_offset + (uint64_t)(e0 + i), wide);
+      store_elem(a.out, e0 + i, dt, cast_one(x, a.fmt, a.rnd, a.flags, true, s, rs, dt == FPEMU_DT_F16, rb));
+    }
+  }
+}
+
+typedef void (*BlockedKernel)(const CastArgs, const int);
+
+template <int FMT, int RND>
+static BlockedKernel pick_blocked_dt(int dt) {
+  switch (dt) {
+    case FPEMU_DT_F32:  return blocked_vec_kernel<FMT, RND, FPEMU_DT_F32>;
+    case FPEMU_DT_F16:  return blocked_vec_kernel<FMT, RND, FPEMU_DT_F16>;
+    default:            return blocked_vec_kernel<FMT, RND, FPEMU_DT_BF16>;
+  }
+}
+template <int FMT>
+static BlockedKernel pick_blocked_rnd(int rnd, int dt) {
+  switch (rnd) {
+    case FPEMU_RND_RNE:        return pick_blocked_dt<FMT, FPEMU_RND_RNE>(dt);
+    case FPEMU_RND_RTZ:        return pick_blocked_dt<FMT, FPEMU_RND_RTZ>(dt);
+    case FPEMU_RND_STOCHASTIC: return pick_blocked_dt<FMT, FPEMU_RND_STOCHASTIC>(dt);
+    default:                   return nullptr;
+  }
+}
+static BlockedKernel pick_blocked(int fmt, int rnd, int dt) {
+  switch (fmt) {
+    case FPEMU_FMT_E5M2: return pick_blocked_rnd<FPEMU_FMT_E5M2>(rnd, dt);
+    case FPEMU_FMT_E4M3: return pick_blocked_rnd<FPEMU_FMT_E4M3>(rnd, dt);
+    case FPEMU_FMT_E3M4: return pick_blocked_rnd<FPEMU_FMT_E3M4>(rnd, dt);
+    default:             return nullptr;
+  }
+}
+
+// ------------------------------------------------------------------------------------------ row-wise
+// One warp per row: pass 1 = |x| max of the row, pass 2 = cast with scale clamp(flt_max / max).  The row is
+// re-read from L1/L2 (rows of Linear/Conv weights are a few KB), so DRAM traffic stays 8 B/elem (fp32).
+template <int FMT, int RND, int DT>
+__global__ void __launch_bounds__(kThreads) rowwise_vec_kernel(const CastArgs a, const int64_t rows, const int64_t cols,
+                                                              const float flt_max, float* d_row_scale, const bool clamp) {
+  constexpr int VE = DtInfo<DT>::kVecElems;
+  const int lane = threadIdx.x & 31;
+  const int64_t warp0 = ((int64_t)blockIdx.x * kThreads + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * kThreads) >> 5;
+  const int64_t vpr = cols / VE;                            // cols % VE == 0 on this path
+  ScaleCtx sc;
+  sc.unscale32 = (a.flags & FPEMU_FLAG_UNSCALE_FP32) != 0;
+  for (int64_t r = warp0; r < rows; r += nwarps) {
+    const char* in = static_cast<const char*>(a.in) + r * cols * DtInfo<DT>::kBytes;
+    char* out = static_cast<char*>(a.out) + r * cols * DtInfo<DT>::kBytes;
+    float m = 0.0f;
+    for (int64_t vi = lane; vi < vpr; vi += 32) {
+      const Vec32 v = *reinterpret_cast<const Vec32*>(in + vi * 32);   // default caching: pass 2 hits L1
+      m = fmaxf(m, vec_absmax<DT>(v));
+    }
+    m = __uint_as_float(warp_max_u32(__float_as_uint(m)));
+    const float s_host = scale_from_amax(m, flt_max, clamp);
+    if (d_row_scale != nullptr && lane == 0) d_row_scale[r] = s_host;
+    const float s = effective_scale(s_host, DT);
+    sc.scale = s;
+    sc.rscale = __frcp_rn(s);
+    for (int64_t vi = lane; vi < vpr; vi += 32) {
+      Vec32 v = *reinterpret_cast<const Vec32*>(in + vi * 32);
+      process_vec<FMT, RND, false, DT, true>(v, sc, a, a.elem_offset + (uint64_t)(r * cols + vi * VE));
+      stg256(out + vi * 32, v);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) rowwise_generic_kernel(const CastArgs a, const int64_t rows, const int64_t cols,
+                                                             const int dt, const float flt_max, float* d_row_scale,
+                                                             const bool clamp) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  const bool wide = (a.fmt == FPEMU_FMT_BF16 || a.fmt == FPEMU_FMT_FP16);
+  for (int64_t r = warp0; r < rows; r += nwarps) {
+    const int64_t e0 = r * cols;
+    float m = 0.0f;
+    for (int64_t i = lane; i < cols; i += 32) m = fmaxf(m, fabsf(load_elem(a.in, e0 + i, dt)));
+    m = __uint_as_float(warp_max_u32(__float_as_uint(m)));
+    const float s_host = scale_from_amax(m, flt_max, clamp);
+    if (d_row_scale != nullptr && lane == 0) d_row_scale[r] = s_host;
+    const float s = effective_scale(s_host, dt);
+    const float rs = __frcp_rn(s);
+    for (int64_t i = lane; i < cols; i += 32) {
+      const float x = load_elem(a.in, e0 + i, dt);
+      uint32_t rb = 0u;
+      if (a.rnd == FPEMU_RND_STOCHASTIC) rb = rand_bits_one(a.seed_lo, a.seed_hi, a.elem_offset + (uint64_t)(e0 + i), wide);
+      store_elem(a.out, e0 + i, dt, cast_one(x, a.fmt, a.rnd, a.flags, true, s, rs, dt == FPEMU_DT_F16, rb));
+    }
+  }
+}
+
+typedef void (*RowwiseKernel)(const CastArgs, const int64_t, const int64_t, const float, float*, const bool);
+
+template <int FMT, int RND>
+static RowwiseKernel pick_rowwise_dt(int dt) {
+  switch (dt) {
+    case FPEMU_DT_F32:  return rowwise_vec_kernel<FMT, RND, FPEMU_DT_F32>;
+    case FPEMU_DT_F16:  return rowwise_vec_kernel<FMT, RND, FPEMU_DT_F16>;
+    default:            return rowwise_vec_kernel<FMT, RND, FPEMU_DT_BF16>;
+  }
+}
+template <int FMT>
+static RowwiseKernel pick_rowwise_rnd(int rnd, int dt) {
+  switch (rnd) {
+    case FPEMU_RND_RNE:        return pick_rowwise_dt<FMT, FPEMU_RND_RNE>(dt);
+    case FPEMU_RND_RTZ:        return pick_rowwise_dt<FMT, FPEMU_RND_RTZ>(dt);
+    case FPEMU_RND_STOCHASTIC: return pick_rowwise_dt<FMT, FPEMU_RND_STOCHASTIC>(dt);
+    default:                   return nullptr;
+  }
+}
+static RowwiseKernel pick_rowwise(int fmt, int rnd, int dt) {
+  switch (fmt) {
+    case FPEMU_FMT_E5M2: return pick_rowwise_rnd<FPEMU_FMT_E5M2>(rnd, dt);
+    case FPEMU_FMT_E4M3: return pick_rowwise_rnd<FPEMU_FMT_E4M3>(rnd, dt);
+    case FPEMU_FMT_E3M4: return pick_rowwise_rnd<FPEMU_FMT_E3M4>(rnd, dt);
+    default:             return nullptr;
+  }
+}
+
+int validate_cast(int64_t n, int dtype, int format, int rounding, float scale, const void* in, const void* out);
+
+static CastArgs make_args(const void* in, void* out, int64_t n, int format, int rounding, int flags, uint64_t seed,
+                          uint64_t elem_offset) {
+  CastArgs a;
+  a.in = in; a.out = out; a.n = n;
+  a.scale = 1.0f; a.d_scale = nullptr;
+  a.seed_lo = (uint32_t)seed; a.seed_hi = (uint32_t)(seed >> 32);
+  a.elem_offset = elem_offset;
+  a.fmt = format; a.rnd = rounding; a.flags = flags;
+  return a;
+}
+
+}  // namespace fpemu
+
+using namespace fpemu;
+
+extern "C" int fpemu_amax(const void* in, int64_t n, int dtype, float* d_amax, void* stream_) {
+  if (n < 0 || d_amax == nullptr || (n > 0 && in == nullptr)) return FPEMU_ERR_ARG;
+  if (dtype < 0 || dtype >= FPEMU_DT_COUNT) return FPEMU_ERR_DTYPE;
+  if ((uintptr_t)in % (uintptr_t)dtype_bytes(dtype)) return FPEMU_ERR_ALIGN;
+  if (n == 0) return FPEMU_OK;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  const int sms = device_info().sm_count;
+  if (((uintptr_t)in & 31u) == 0) {
+    const int ve = dtype == FPEMU_DT_F32 ? 8 : 16;
+    const int64_t per_cta = (int64_t)kAmaxThreads * kAmaxUnroll;
+    int64_t want = (n / ve + per_cta - 1) / per_cta;
+    if (want < 1) want = 1;
+    const int64_t cap = (int64_t)sms * 8;
+    const int grid = (int)(want < cap ? want : cap);
+    switch (dtype) {
+      case FPEMU_DT_F32:  amax_kernel<FPEMU_DT_F32><<<grid, kAmaxThreads, 0, stream>>>(in, n, d_amax); break;
+      case FPEMU_DT_F16:  amax_kernel<FPEMU_DT_F16><<<grid, kAmaxThreads, 0, stream>>>(in, n, d_amax); break;
+      default:            amax_kernel<FPEMU_DT_BF16><<<grid, kAmaxThreads, 0, stream>>>(in, n, d_amax); break;
+    }
+  } else {
+    int64_t want = (n + 255) / 256;
+    const int64_t cap = (int64_t)sms * 8;
+    amax_generic_kernel<<<(int)(want < cap ? want : cap), 256, 0, stream>>>(in, n, dtype, d_amax);
+  }
+  return (int)cudaGetLastError();
+}
+
+extern "C" int fpemu_scale_from_amax(const float* d_amax, int count, float flt_max, float* d_scale, void* stream_) {
+  if (count < 0 || (count > 0 && (d_amax == nullptr || d_scale == nullptr))) return FPEMU_ERR_ARG;
+  if (count == 0) return FPEMU_OK;
+  scale_from_amax_kernel<<<(count + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream_)>>>(d_amax, count, flt_max, d_scale);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int fpemu_cast_blocked(const void* in, void* out, int64_t n, int64_t block_size, int dtype, int format,
+                                  int rounding, int flags, uint64_t seed, uint64_t elem_offset, void* stream_) {
+  int st = validate_cast(n, dtype, format, rounding, 1.0f, in, out);
+  if (st != FPEMU_OK) return st;
+  // BFLOAT16 / FLOAT16 / E5M2_DAZ kernels of the reference take no block_norm argument
+  if (format == FPEMU_FMT_BF16 || format == FPEMU_FMT_FP16 || (flags & FPEMU_FLAG_DAZ)) return FPEMU_ERR_MODE;
+  if (block_size <= 0 || (n % block_size) != 0) return FPEMU_ERR_ARG;
+  if (n == 0) return FPEMU_OK;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  const CastArgs a = make_args(in, out, n, format, rounding, flags, seed, elem_offset);
+  const int sms = device_info().sm_count;
+  const int ve = dtype == FPEMU_DT_F32 ? 8 : 16;
+  const bool aligned = (((uintptr_t)in | (uintptr_t)out) & 31u) == 0;
+  const bool rng_ok = (rounding != FPEMU_RND_STOCHASTIC) || ((elem_offset & 15u) == 0);
+  const int64_t vpb = block_size / ve;
+  BlockedKernel k = nullptr;
+  if (aligned && rng_ok && block_size % ve == 0 && vpb <= 32 && (vpb & (vpb - 1)) == 0)
+    k = pick_blocked(format, rounding, dtype);
+  if (k != nullptr) {
+    int64_t want = (n / ve + kThreads - 1) / kThreads;
+    const int64_t cap = (int64_t)sms * 16;
+    k<<<(int)(want < cap ? want : cap), kThreads, 0, stream>>>(a, (int)vpb);
+  } else {
+    int64_t want = (n / block_size + 7) / 8;                 // 8 warps per CTA, one warp per block
+    const int64_t cap = (int64_t)sms * 8;
+    blocked_generic_kernel<<<(int)(want < cap ? want : cap), 256, 0, stream>>>(a, block_size, dtype);
+  }
+  return (int)cudaGetLastError();
+}
+
+extern "C" int fpemu_cast_rowwise(const void* in, void* out, int64_t rows, int64_t cols, int dtype, int format,
+                                  int rounding, int flags, float flt_max, float* d_row_scale, uint64_t seed,
+                                  uint64_t elem_offset, void* stream_) {
+  if (rows < 0 || cols < 0) return FPEMU_ERR_ARG;
+  const int64_t n = rows * cols;
+  int st = validate_cast(n, dtype, format, rounding, 1.0f, in, out);
+  if (st != FPEMU_OK) return st;
+  if (format == FPEMU_FMT_BF16 || format == FPEMU_FMT_FP16) return FPEMU_ERR_MODE;   // these take no scale
+  if (n == 0) return FPEMU_OK;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  const bool clamp = (flags & FPEMU_FLAG_NO_SCALE_CLAMP) == 0;
+  const CastArgs a = make_args(in, out, n, format, rounding, flags, seed, elem_offset);
+  const int sms = device_info().sm_count;
+  const int ve = dtype == FPEMU_DT_F32 ? 8 : 16;
+  const bool aligned = (((uintptr_t)in | (uintptr_t)out) & 31u) == 0 && cols % ve == 0;
+  const bool rng_ok = (rounding != FPEMU_RND_STOCHASTIC) || ((elem_offset & 15u) == 0 && cols % 16 == 0);
+  RowwiseKernel k = (aligned && rng_ok && (flags & FPEMU_FLAG_DAZ) == 0) ? pick_rowwise(format, rounding, dtype) : nullptr;
+  int64_t want = (rows + 7) / 8;                             // 8 warps per CTA, one warp per row
+  const int64_t cap = (int64_t)sms * 8;
+  const int grid = (int)(want < cap ? want : cap);
+  if (k != nullptr) k<<<grid, kThreads, 0, stream>>>(a, rows, cols, flt_max, d_row_scale, clamp);
+  else rowwise_generic_kernel<<<grid, 256, 0, stream>>>(a, rows, cols, dtype, flt_max, d_row_scale, clamp);
+  return (int)cudaGetLastError();
+}

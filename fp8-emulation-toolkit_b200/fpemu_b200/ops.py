@@ -1,0 +1,197 @@
+"""Tensor-level operations over the C ABI.  PyTorch is plumbing here (device memory, streams); every
+number is produced by the CUDA kernels of libfpemu_b200.so."""
+import itertools
+
+import torch
+
+from . import _lib as L
+
+_DT = {torch.float32: L.DT_F32, torch.float16: L.DT_F16, torch.bfloat16: L.DT_BF16}
+
+# flt_max per format, mpemu/qutils.py:100-114
+FLT_MAX = {L.FMT_E5M2: 57344.0, L.FMT_E4M3: 448.0, L.FMT_E4M3_IEEE: 240.0, L.FMT_E3M4: 30.0, L.FMT_FP4: 1.0}
+
+_seed_base = 42           # the reference seeds torch with 42 at import (cuda/fpemu.py:19); we keep our own stream
+_seed_counter = itertools.count()
+
+
+def manual_seed(seed):
+    """Reset the stochastic-rounding seed sequence (one fresh Philox key per stochastic call)."""
+    global _seed_base, _seed_counter
+    _seed_base = int(seed) & 0xFFFFFFFF
+    _seed_counter = itertools.count()
+
+
+def next_seed():
+    return (_seed_base << 32) | (next(_seed_counter) & 0xFFFFFFFF)
+
+
+def _dt(t):
+    try:
+        return _DT[t.dtype]
+    except KeyError:
+        raise TypeError("fpemu: unsupported dtype %s (float32, float16, bfloat16)" % t.dtype)
+
+
+def _check_tensor(t, name="input"):
+    if not t.is_cuda:
+        raise RuntimeError("%s must be a CUDA tensor" % name)           # CHECK_CUDA, cuda/fpemu_impl.cpp:23
+    if not t.is_contiguous():
+        raise RuntimeError("%s must be contiguous" % name)              # CHECK_CONTIGUOUS, :24
+
+
+def _stream(t):
+    return torch.cuda.current_stream(t.device).cuda_stream
+
+
+class _on_device(object):
+    """Make t's device current for the duration of a launch (cheap no-op when it already is)."""
+    def __init__(self, t):
+        self.idx = t.device.index
+        self.prev = None
+
+    def __enter__(self):
+        cur = torch.cuda.current_device()
+        if self.idx is not None and cur != self.idx:
+            self.prev = cur
+            torch.cuda.set_device(self.idx)
+
+    def __exit__(self, *exc):
+        if self.prev is not None:
+            torch.cuda.set_device(self.prev)
+
+
+def cast(x, mode, out=None, scale=1.0, d_scale=None, seed=None, elem_offset=0, n=None, unscale_fp32=False):
+    """QDQ-cast `x` (CUDA, contiguous) into `out` (default: new tensor; pass out=x for in-place).
+    `d_scale`: optional 1-element float32 CUDA tensor used instead of `scale` (no host sync)."""
+    _check_tensor(x)
+    fmt, rnd, flags = L.parse_mode(mode)
+    if unscale_fp32:
+        flags |= L.FLAG_UNSCALE_FP32
+    if out is None:
+        out = torch.empty_like(x)
+    else:
+        _check_tensor(out, "out")
+        if out.dtype != x.dtype or out.numel() < (x.numel() if n is None else n):
+            raise ValueError("fpemu: out must match input dtype and size")
+    n = x.numel() if n is None else int(n)
+    if n > x.numel():
+        raise ValueError("fpemu: size larger than the tensor")
+    if rnd == L.RND_STOCHASTIC and seed is None:
+        seed = next_seed()
+    dptr = None
+    if d_scale is not None:
+        if not (d_scale.is_cuda and d_scale.dtype == torch.float32 and d_scale.numel() >= 1):
+            raise ValueError("fpemu: d_scale must be a float32 CUDA tensor")
+        dptr = d_scale.data_ptr()
+    with _on_device(x):
+        st = L.lib().fpemu_cast(x.data_ptr(), out.data_ptr(), n, _dt(x), fmt, rnd, flags, float(scale), dptr,
+                                int(seed or 0), int(elem_offset), _stream(x))
+    L.check(st, "fpemu_cast(%s)" % mode)
+    return out
+
+
+def cast_blocked(x, mode, block_size, out=None, seed=None, elem_offset=0, n=None, unscale_fp32=False):
+    _check_tensor(x)
+    fmt, rnd, flags = L.parse_mode(mode)
+    if unscale_fp32:
+        flags |= L.FLAG_UNSCALE_FP32
+    if out is None:
+        out = torch.empty_like(x)
+    n = x.numel() if n is None else int(n)
+    if rnd == L.RND_STOCHASTIC and seed is None:
+        seed = next_seed()
+    with _on_device(x):
+        st = L.lib().fpemu_cast_blocked(x.data_ptr(), out.data_ptr(), n, int(block_size), _dt(x), fmt, rnd, flags,
+                                        int(seed or 0), int(elem_offset), _stream(x))
+    L.check(st, "fpemu_cast_blocked(%s, %d)" % (mode, block_size))
+    return out
+
+
+def amax(x, out=None, n=None):
+    """max|x| as a 1-element float32 CUDA tensor, max-accumulated into `out` when given (no host sync)."""
+    _check_tensor(x)
+    if out is None:
+        out = torch.zeros(1, dtype=torch.float32, device=x.device)
+    n = x.numel() if n is None else int(n)
+    with _on_device(x):
+        st = L.lib().fpemu_amax(x.data_ptr(), n, _dt(x), out.data_ptr(), _stream(x))
+    L.check(st, "fpemu_amax")
+    return out
+
+
+def scale_from_amax(d_amax, flt_max, out=None):
+    """clamp(flt_max / amax) on the device (qutils.py:283-285), elementwise over a float32 CUDA vector."""
+    if out is None:
+        out = torch.empty_like(d_amax)
+    with _on_device(d_amax):
+        st = L.lib().fpemu_scale_from_amax(d_amax.data_ptr(), d_amax.numel(), float(flt_max), out.data_ptr(),
+                                           _stream(d_amax))
+    L.check(st, "fpemu_scale_from_amax")
+    return out
+
+
+def cast_amax_scaled(x, mode, out=None, flt_max=None, seed=None, elem_offset=0, unscale_fp32=False,
+                     d_amax=None, return_scale=False):
+    """Per-tensor amax-scaled cast without a host sync: amax kernel -> scale kernel -> cast kernel, all on the
+    current stream (the `per-tensor` / `max` branch of quantize_tensor, qutils.py:274-287).
+    `d_amax` lets a caller supply an already reduced (e.g. all-reduced across ranks) amax."""
+    fmt, _, _ = L.parse_mode(mode)
+    if flt_max is None:
+        flt_max = FLT_MAX[fmt]
+    if d_amax is None:
+        d_amax = amax(x)
+    d_scale = scale_from_amax(d_amax, flt_max)
+    y = cast(x, mode, out=out, d_scale=d_scale, seed=seed, elem_offset=elem_offset, unscale_fp32=unscale_fp32)
+    return (y, d_scale) if return_scale else y
+
+
+def cast_rowwise(x2d, mode, out=None, flt_max=None, clamp=True, seed=None, elem_offset=0, unscale_fp32=False,
+                 return_scales=False, rows=None, cols=None):
+    """Per-channel (dim-0) amax-scaled cast in ONE launch (replaces the loop of qutils.py:289-311)."""
+    _check_tensor(x2d)
+    fmt, rnd, flags = L.parse_mode(mode)
+    if unscale_fp32:
+        flags |= L.FLAG_UNSCALE_FP32
+    if not clamp:
+        flags |= L.FLAG_NO_SCALE_CLAMP
+    if flt_max is None:
+        flt_max = FLT_MAX[fmt]
+    if rows is None:
+        rows = x2d.shape[0] if x2d.dim() > 0 else 1
+        cols = x2d.numel() // max(rows, 1)
+    if out is None:
+        out = torch.empty_like(x2d)
+    scales = torch.empty(rows, dtype=torch.float32, device=x2d.device) if return_scales else None
+    if rnd == L.RND_STOCHASTIC and seed is None:
+        seed = next_seed()
+    with _on_device(x2d):
+        st = L.lib().fpemu_cast_rowwise(x2d.data_ptr(), out.data_ptr(), int(rows), int(cols), _dt(x2d), fmt, rnd,
+                                        flags, float(flt_max), scales.data_ptr() if scales is not None else None,
+                                        int(seed or 0), int(elem_offset), _stream(x2d))
+    L.check(st, "fpemu_cast_rowwise(%s)" % mode)
+    return (out, scales) if return_scales else out
+
+
+class HostCaster(object):
+    """Host-buffer cast (pinned in, pinned out) pipelined through two device staging buffers.
+    Owns the staging buffers and three streams; `run` is what the end-to-end benchmark times."""
+
+    def __init__(self, dtype=torch.float32, chunk_elems=1 << 24, device=None):
+        self.device = torch.device("cuda", torch.cuda.current_device() if device is None else device)
+        self.dtype = dtype
+        self.chunk = int(chunk_elems) // 16 * 16
+        self.stage = [torch.empty(self.chunk, dtype=dtype, device=self.device) for _ in range(2)]
+        self.streams = [torch.cuda.Stream(self.device) for _ in range(3)]
+
+    def run(self, h_in, h_out, mode, scale=1.0, seed=0):
+        if h_in.is_cuda or h_out.is_cuda:
+            raise ValueError("HostCaster.run takes host tensors")
+        fmt, rnd, flags = L.parse_mode(mode)
+        with _on_device(self.stage[0]):
+            st = L.lib().fpemu_cast_host(h_in.data_ptr(), h_out.data_ptr(), h_in.numel(), _DT[self.dtype], fmt, rnd,
+                                         flags, float(scale), int(seed), self.stage[0].data_ptr(),
+                                         self.stage[1].data_ptr(), self.chunk, self.streams[0].cuda_stream,
+                                         self.streams[1].cuda_stream, self.streams[2].cuda_stream)
+        L.check(st, "fpemu_cast_host(%s)" % mode)
+        return h_out

@@ -18,6 +18,12 @@
 
 #include <stdint.h>
 
+#if defined(__GNUC__)
+#define FPEMU_API __attribute__((visibility("default")))
+#else
+#define FPEMU_API
+#endif
+
 #ifdef __cplusplus
 extern "C" {
 #endif
@@ -52,10 +58,12 @@ enum {
 /* Flags. */
 enum {
   FPEMU_FLAG_DAZ = 1,          /* denormal flush variants: E5M2_DAZ_*, FLOAT16_DAZ_RNE               */
-  FPEMU_FLAG_UNSCALE_FP32 = 2  /* multiply by 1/scale in fp32 like the reference CPU op
+  FPEMU_FLAG_UNSCALE_FP32 = 2, /* multiply by 1/scale in fp32 like the reference CPU op
                                   (cpp/fpemu_impl.cpp:761,1131,1716).  Default (flag clear) rounds the
                                   un-scaled value through fp16 like the reference CUDA op
                                   (fpemu_kernels.cu:461,539,652,982).                                 */
+  FPEMU_FLAG_NO_SCALE_CLAMP = 4 /* fpemu_cast_rowwise only: skip the `6.55e4 if scale > 3.275e4` clamp,
+                                  as the fine-grained branch of quantize_tensor does (qutils.py:328-330)  */
 };
 
 /* Element types of the in/out buffers (both buffers always share one type). */
@@ -73,17 +81,17 @@ enum {
 };
 
 /* Library version (major*10000 + minor*100 + patch). */
-int fpemu_version(void);
+FPEMU_API int fpemu_version(void);
 
 /* Text for a status returned by any entry point (static storage, never NULL). */
-const char* fpemu_strerror(int status);
+FPEMU_API const char* fpemu_strerror(int status);
 
 /* Parse a reference mode string ("E4M3_RNE", "E5M2_DAZ_STOCHASTIC", "BFLOAT16_RNE", ...) into
  * (format, rounding, flags).  Replaces the `mode.compare(...)` chain of fpemu_cuda_forward,
  * fpemu_kernels.cu:1058-1364.  Besides the reference's strings it accepts <FMT>_RTZ for E4M3, E3M4,
  * BFLOAT16 (truncate = "same pipeline, rounding add 0").  Unknown strings return
  * FPEMU_ERR_MODE (the reference silently returns zeros, :1375-1380). */
-int fpemu_parse_mode(const char* mode, int* format, int* rounding, int* flags);
+FPEMU_API int fpemu_parse_mode(const char* mode, int* format, int* rounding, int* flags);
 
 /* Elementwise quantize-dequantize cast of n elements: out[i] = QDQ(in[i]).  in == out is allowed
  * (in-place).  Replaces the kernel launches of fpemu_cuda_forward (fpemu_kernels.cu:1028-1381) for
@@ -94,7 +102,7 @@ int fpemu_parse_mode(const char* mode, int* format, int* rounding, int* flags);
  *   seed, elem_offset  stochastic rounding uses Philox4x32-10 keyed by seed with the counter derived
  *            from (elem_offset + i), so a tensor cast in slabs gives the same bits as in one piece.
  */
-int fpemu_cast(const void* in, void* out, int64_t n, int dtype, int format, int rounding, int flags,
+FPEMU_API int fpemu_cast(const void* in, void* out, int64_t n, int dtype, int format, int rounding, int flags,
                float scale, const float* d_scale, uint64_t seed, uint64_t elem_offset, void* stream);
 
 /* Blocked cast ("block_norm"): every run of block_size consecutive elements gets its own power-of-two
@@ -102,23 +110,24 @@ int fpemu_cast(const void* in, void* out, int64_t n, int dtype, int format, int 
  * E4M3_IEEE), 1 (E3M4); FP4 uses 1/max.  Replaces absmax_block + the per-kernel scale derivation,
  * fpemu_kernels.cu:150-170, :407-414, :575-582, :905-912.  n must be a multiple of block_size
  * (the reference silently disables blocking otherwise, :1048-1051; this ABI returns FPEMU_ERR_ARG and
- * leaves that policy to the caller). */
-int fpemu_cast_blocked(const void* in, void* out, int64_t n, int64_t block_size, int dtype, int format,
+ * leaves that policy to the caller).  Formats whose reference kernels take no block_norm argument
+ * (BFLOAT16, FLOAT16, E5M2_DAZ) return FPEMU_ERR_MODE. */
+FPEMU_API int fpemu_cast_blocked(const void* in, void* out, int64_t n, int64_t block_size, int dtype, int format,
                        int rounding, int flags, uint64_t seed, uint64_t elem_offset, void* stream);
 
 /* Single-pass absolute maximum of n elements, max-accumulated into *d_amax (device float the caller
  * initialised, normally to 0; NaN inputs are ignored like torch.max on |x| never is — see DESIGN.md).
  * Replaces `torch.max(torch.abs(tensor.flatten()))` of mpemu/qutils.py:282. */
-int fpemu_amax(const void* in, int64_t n, int dtype, float* d_amax, void* stream);
+FPEMU_API int fpemu_amax(const void* in, int64_t n, int dtype, float* d_amax, void* stream);
 
 /* d_scale[i] = clamp(flt_max / d_amax[i]) for i < count, with the reference's clamp
  * `scale = 6.55e4 if scale > 3.275e4` (mpemu/qutils.py:283-285).  Device-side, no host sync. */
-int fpemu_scale_from_amax(const float* d_amax, int count, float flt_max, float* d_scale, void* stream);
+FPEMU_API int fpemu_scale_from_amax(const float* d_amax, int count, float flt_max, float* d_scale, void* stream);
 
 /* Row-wise (per-channel) amax-scaled cast of a rows x cols row-major matrix: each row gets
  * scale = clamp(flt_max / max|row|).  One launch replaces the Python per-channel loop of
  * mpemu/qutils.py:289-311.  d_row_scale (optional, rows floats) receives the scales used. */
-int fpemu_cast_rowwise(const void* in, void* out, int64_t rows, int64_t cols, int dtype, int format,
+FPEMU_API int fpemu_cast_rowwise(const void* in, void* out, int64_t rows, int64_t cols, int dtype, int format,
                        int rounding, int flags, float flt_max, float* d_row_scale, uint64_t seed,
                        uint64_t elem_offset, void* stream);
 
@@ -127,7 +136,7 @@ int fpemu_cast_rowwise(const void* in, void* out, int64_t rows, int64_t cols, in
  * buffers of chunk_elems elements each (d_stage[0], d_stage[1]) so the H2D copy, the kernel and the
  * D2H copy of consecutive chunks overlap on the three streams given.  Synchronises the three streams
  * before returning. */
-int fpemu_cast_host(const void* h_in, void* h_out, int64_t n, int dtype, int format, int rounding,
+FPEMU_API int fpemu_cast_host(const void* h_in, void* h_out, int64_t n, int dtype, int format, int rounding,
                     int flags, float scale, uint64_t seed, void* d_stage0, void* d_stage1,
                     int64_t chunk_elems, void* stream_h2d, void* stream_compute, void* stream_d2h);
 

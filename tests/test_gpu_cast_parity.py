@@ -1,0 +1,381 @@
+"""GPU parity tests proper: the CUDA path, called through the C ABI (fpemu_b200.ops -> ctypes ->
+libfpemu_b200.so), against
+  (a) the C oracle (oracle/fpemu_oracle.c) on the same seeded inputs,
+  (b) the committed golden vectors the reference CPU op produced (tests/golden/),
+  (c) the reference's own CUDA kernels compiled unmodified for sm_100a (oracle/_ref/fpemu_cuda_ref.so),
+bit-exact for every deterministic mode (NaN compared as NaN: payloads are ISA-specific)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import fpemu_oracle as O
+from oracle import ref_loader
+
+pytestmark = pytest.mark.gpu
+
+DET_MODES = ["E5M2_RTZ", "E5M2_RNE", "E5M2_RNAZ", "E5M2_RNTZ", "E5M2_RPINF", "E5M2_RNINF",
+             "E5M2_DAZ_RNE", "E5M2_DAZ_RNAZ", "E5M2_DAZ_RNTZ", "E4M3_RNE", "E3M4_RNE",
+             "FLOAT16_RNE", "FLOAT16_DAZ_RNE", "BFLOAT16_RNE", "E4M3_RTZ", "E3M4_RTZ", "BFLOAT16_RTZ",
+             "E4M3_IEEE_RNE", "FP4_NEAREST"]
+GOLDEN_MODES = ["E5M2_RTZ", "E5M2_RNE", "E5M2_RNAZ", "E5M2_RNTZ", "E5M2_RPINF", "E5M2_RNINF",
+                "E5M2_DAZ_RNE", "E5M2_DAZ_RNAZ", "E5M2_DAZ_RNTZ", "E4M3_RNE", "E3M4_RNE",
+                "FLOAT16_RNE", "FLOAT16_DAZ_RNE"]
+SR_MODES = ["E5M2_STOCHASTIC", "E5M2_DAZ_STOCHASTIC", "E4M3_STOCHASTIC", "E3M4_STOCHASTIC",
+            "BFLOAT16_STOCHASTIC", "FLOAT16_STOCHASTIC"]
+SCALES = [1.0, 0.125, 3.7, 94.09]
+
+
+@pytest.fixture(scope="module")
+def F():
+    import fpemu_b200
+    fpemu_b200._lib.lib()          # raises if the CUDA library is missing: no fallback
+    return fpemu_b200
+
+
+@pytest.fixture(autouse=True)
+def _cuda_nan_mode():
+    O.set_nan_mode(False)
+    yield
+
+
+def dev(x):
+    return torch.from_numpy(np.ascontiguousarray(x)).cuda()
+
+
+def host(t):
+    if t.dtype == torch.bfloat16:
+        return t.view(torch.int16).cpu().numpy().view(np.uint16)
+    return t.cpu().numpy()
+
+
+def assert_same(got, want, what):
+    ok = O.same_bits_or_both_nan(got, want)
+    if not ok.all():
+        bad = np.nonzero(~ok)[0]
+        i = bad[0]
+        raise AssertionError("%s: %d / %d mismatches, first at %d: got %r want %r" %
+                             (what, len(bad), ok.size, i, got.flat[i], want.flat[i]))
+
+
+def fp16_patterns():
+    return np.arange(65536, dtype=np.uint16).view(np.float16).astype(np.float32)
+
+
+def wide(n=1 << 16, seed=11):
+    rng = np.random.default_rng(seed)
+    x = rng.standard_normal(n).astype(np.float32) * np.exp2(rng.integers(-30, 20, n)).astype(np.float32)
+    spec = np.array([0.0, -0.0, np.inf, -np.inf, np.nan, -np.nan, 1e-40, -1e-40, 65504, 65520, -65520, 3.4e38, 1e-45,
+                     448, 464, 480, -448, 30, 31, -31, 57344, 61440, -61440], dtype=np.float32)
+    x[:len(spec)] = spec
+    return x
+
+
+# ------------------------------------------------------------------------------------------ vs oracle
+@pytest.mark.parametrize("mode", DET_MODES)
+def test_exhaustive_fp16_patterns_vs_oracle(F, mode):
+    x = fp16_patterns()
+    got = host(F.cast(dev(x), mode))
+    assert_same(got, O.cast(x, mode), mode)
+
+
+@pytest.mark.parametrize("mode", DET_MODES)
+@pytest.mark.parametrize("scale", SCALES)
+def test_wide_vs_oracle_both_unscale_semantics(F, mode, scale):
+    if mode.startswith(("FLOAT16", "BFLOAT16")) and scale != 1.0:
+        pytest.skip("format takes no scale")
+    x = wide()
+    for fp32_unscale in (False, True):
+        got = host(F.cast(dev(x), mode, scale=scale, unscale_fp32=fp32_unscale))
+        assert_same(got, O.cast(x, mode, scale=scale, unscale_fp32=fp32_unscale), "%s s=%g fp32=%s" % (mode, scale, fp32_unscale))
+
+
+@pytest.mark.parametrize("mode", DET_MODES)
+@pytest.mark.parametrize("dtype", ["f16", "bf16"])
+def test_half_and_bfloat_tensors_vs_oracle(F, mode, dtype):
+    rng = np.random.default_rng(5)
+    if dtype == "f16":
+        xb = rng.integers(0, 65536, 1 << 16).astype(np.uint16)
+        xb[:65536] = np.arange(65536, dtype=np.uint16)           # every fp16 pattern
+        x_np = xb.view(np.float16)
+        xt = dev(x_np)
+    else:
+        x_np = np.arange(65536, dtype=np.uint16)                 # every bf16 pattern (uint16 = bf16 bits)
+        xt = dev(x_np.view(np.int16)).view(torch.bfloat16)
+    for scale in (1.0, 3.7):
+        if mode.startswith(("FLOAT16", "BFLOAT16")) and scale != 1.0:
+            continue
+        got = host(F.cast(xt, mode, scale=scale))
+        assert_same(got, O.cast(x_np, mode, scale=scale), "%s %s s=%g" % (mode, dtype, scale))
+
+
+# ------------------------------------------------------------------------------------------ vs golden
+@pytest.mark.parametrize("mode", GOLDEN_MODES)
+def test_golden_fp16_patterns(F, golden_dir, mode):
+    g = np.load(os.path.join(golden_dir, "fp16_patterns.npz"))
+    x = fp16_patterns()
+    want = g[mode].view(np.float16).astype(np.float32)
+    got = host(F.cast(dev(x), mode, unscale_fp32=True))
+    ok = O.same_bits_or_both_nan(got, want)
+    ok |= np.isnan(x) & np.signbit(x)        # -NaN: x86 keeps the sign through float->half, CUDA does not
+    assert ok.all(), "%s: %d mismatches" % (mode, (~ok).sum())
+
+
+@pytest.mark.parametrize("mode", GOLDEN_MODES)
+def test_golden_wide_all_scales_cpu_unscale(F, golden_dir, mode):
+    g = np.load(os.path.join(golden_dir, "wide.npz"))
+    x = g["input"].view(np.float32)
+    xt = dev(x)
+    for key in g.files:
+        if not key.startswith(mode + "@"):
+            continue
+        scale = float(key.split("@")[1])
+        got = host(F.cast(xt, mode, scale=scale, unscale_fp32=True))
+        ok = O.same_bits_or_both_nan(got, g[key].view(np.float32))
+        ok |= np.isnan(x) & np.signbit(x)
+        assert ok.all(), "%s s=%g: %d mismatches" % (mode, scale, (~ok).sum())
+
+
+def test_golden_bf16(F, golden_dir):
+    g = np.load(os.path.join(golden_dir, "wide.npz"))
+    if "BFLOAT16_RNE@1" not in g.files:
+        pytest.skip("no bf16 fixture")
+    x = g["bf16_input"].view(np.float32)
+    got = host(F.cast(dev(x), "BFLOAT16_RNE"))
+    ok = O.same_bits_or_both_nan(got, g["BFLOAT16_RNE@1"].view(np.float32)) | (x == 0)
+    assert ok.all()
+
+
+@pytest.mark.parametrize("mode", ["E5M2_RNE", "E4M3_RNE", "E3M4_RNE", "E5M2_RTZ"])
+@pytest.mark.parametrize("bs", [32, 64, 1024])
+def test_golden_blocked(F, golden_dir, mode, bs):
+    g = np.load(os.path.join(golden_dir, "blocked.npz"))
+    x = g["input"].view(np.float32)
+    got = host(F.cast_blocked(dev(x), mode, bs, unscale_fp32=True))
+    assert_same(got, g["%s@%d" % (mode, bs)].view(np.float32), "%s bs=%d" % (mode, bs))
+
+
+# ------------------------------------------------------------------------------------------ vs reference CUDA kernels
+REF_CUDA_MODES = ["E5M2_RTZ", "E5M2_RNE", "E5M2_RNAZ", "E5M2_RNTZ", "E5M2_RPINF", "E5M2_RNINF",
+                  "E5M2_DAZ_RNE", "E5M2_DAZ_RNAZ", "E5M2_DAZ_RNTZ", "E4M3_RNE", "E3M4_RNE", "E4M3_IEEE_RNE",
+                  "FLOAT16_RNE", "FLOAT16_DAZ_RNE", "BFLOAT16_RNE", "FP4_NEAREST"]
+
+
+@pytest.fixture(scope="module")
+def ref_cuda():
+    if not ref_loader.available("fpemu_cuda_ref"):
+        pytest.skip("oracle/_ref/fpemu_cuda_ref.so not built")
+    return ref_loader.load("fpemu_cuda_ref")
+
+
+@pytest.mark.parametrize("mode", REF_CUDA_MODES)
+def test_bit_exact_vs_reference_cuda_kernels(F, ref_cuda, mode):
+    for name, x in (("fp16pat", fp16_patterns()), ("wide", wide())):
+        xt = dev(x)
+        for scale in SCALES:
+            if mode.startswith(("FLOAT16", "BFLOAT16")) and scale != 1.0:
+                continue
+            want = ref_cuda.forward(xt.clone(), mode, xt.numel(), False, scale, False, 1)[0]
+            got = F.cast(xt, mode, scale=scale)
+            assert_same(host(got), host(want), "%s %s s=%g" % (mode, name, scale))
+
+
+@pytest.mark.parametrize("mode", ["E5M2_RNE", "E4M3_RNE", "E3M4_RNE", "E5M2_DAZ_RNE", "FLOAT16_RNE", "BFLOAT16_RNE"])
+def test_bit_exact_vs_reference_cuda_kernels_half_tensors(F, ref_cuda, mode):
+    xt = dev(np.arange(65536, dtype=np.uint16).view(np.float16))
+    for scale in (1.0, 0.125, 3.7):
+        if mode.startswith(("FLOAT16", "BFLOAT16")) and scale != 1.0:
+            continue
+        want = ref_cuda.forward(xt.clone(), mode, xt.numel(), False, scale, False, 1)[0]
+        got = F.cast(xt, mode, scale=scale)
+        assert_same(host(got), host(want), "%s half s=%g" % (mode, scale))
+
+
+@pytest.mark.parametrize("mode", ["E5M2_RNE", "E4M3_RNE", "E3M4_RNE"])
+@pytest.mark.parametrize("bs", [32, 64, 256, 1024])
+def test_blocked_vs_reference_cuda_kernels(F, ref_cuda, mode, bs):
+    # power-of-two block sizes only: the reference's smem tree over-reads otherwise
+    rng = np.random.default_rng(2)
+    x = (rng.standard_normal(1 << 16).astype(np.float32) * np.repeat(np.exp2(rng.integers(-6, 6, 64)), 1024).astype(np.float32))
+    xt = dev(x)
+    want = ref_cuda.forward(xt.clone(), mode, xt.numel(), False, 1.0, True, bs)[0]
+    got = F.cast_blocked(xt, mode, bs)
+    assert_same(host(got), host(want), "%s bs=%d" % (mode, bs))
+
+
+# ------------------------------------------------------------------------------------------ shapes, alignment, in-place
+@pytest.mark.parametrize("n", [0, 1, 7, 8, 9, 15, 16, 17, 31, 255, 1000003])
+@pytest.mark.parametrize("mode", ["E4M3_RNE", "E5M2_STOCHASTIC", "BFLOAT16_RNE"])
+def test_ragged_sizes(F, mode, n):
+    x = wide(max(n, 1), seed=n)[:n]
+    got = host(F.cast(dev(x), mode, seed=7, scale=1.0)) if n else np.zeros(0, np.float32)
+    if n:
+        assert_same(got, O.cast(x, mode, seed=7), "%s n=%d" % (mode, n))
+    for dt in (torch.float16, torch.bfloat16):
+        xt = dev(x).to(dt)
+        y = F.cast(xt, mode, seed=7)
+        x_np = host(xt)
+        assert_same(host(y), O.cast(x_np, mode, seed=7), "%s n=%d %s" % (mode, n, dt))
+
+
+@pytest.mark.parametrize("mode", ["E4M3_RNE", "E3M4_STOCHASTIC", "E5M2_RNE"])
+def test_unaligned_views_take_the_generic_kernel(F, mode):
+    x = wide(4099)
+    xt = dev(x)
+    for off in (1, 3, 5):
+        sub = xt[off:]
+        out = torch.empty_like(xt)[off:]
+        F.cast(sub, mode, out=out, seed=3, scale=3.7)
+        assert_same(host(out), O.cast(x[off:], mode, seed=3, scale=3.7), "%s off=%d" % (mode, off))
+
+
+@pytest.mark.parametrize("mode", ["E4M3_RNE", "E5M2_RNE", "E3M4_RNE", "BFLOAT16_RNE", "E4M3_STOCHASTIC"])
+@pytest.mark.parametrize("dt", [torch.float32, torch.float16, torch.bfloat16])
+def test_inplace_equals_out_of_place(F, mode, dt):
+    xt = dev(wide(100003)).to(dt)
+    a = F.cast(xt, mode, seed=9, scale=2.5)
+    b = xt.clone()
+    r = F.cast(b, mode, out=b, seed=9, scale=2.5)
+    assert r.data_ptr() == b.data_ptr()
+    assert_same(host(a), host(b), mode)
+
+
+# ------------------------------------------------------------------------------------------ stochastic rounding
+@pytest.mark.parametrize("mode", SR_MODES)
+@pytest.mark.parametrize("dt", ["f32", "f16", "bf16"])
+def test_stochastic_bits_match_oracle_given_the_documented_philox_stream(F, mode, dt):
+    x = wide(1 << 15, seed=21)
+    xt = dev(x)
+    if dt == "f16":
+        xt = xt.half()
+    elif dt == "bf16":
+        xt = xt.bfloat16()
+    x_np = host(xt)
+    for scale in (1.0, 3.7):
+        if mode.startswith(("FLOAT16", "BFLOAT16")) and scale != 1.0:
+            continue
+        got = host(F.cast(xt, mode, seed=0xC0FFEE1234, scale=scale))
+        assert_same(got, O.cast(x_np, mode, seed=0xC0FFEE1234, scale=scale), "%s %s s=%g" % (mode, dt, scale))
+
+
+@pytest.mark.parametrize("mode", ["E5M2_STOCHASTIC", "E4M3_STOCHASTIC", "BFLOAT16_STOCHASTIC"])
+def test_stochastic_is_partition_independent(F, mode):
+    x = dev(wide(1 << 16, seed=4))
+    whole = F.cast(x, mode, seed=77)
+    for cut in (16 * 1000, 16 * 1000 + 8, 12345):       # aligned, half-aligned, arbitrary slab boundary
+        a = F.cast(x[:cut].clone(), mode, seed=77, elem_offset=0)
+        b = F.cast(x[cut:].clone(), mode, seed=77, elem_offset=cut)
+        assert_same(host(torch.cat([a, b])), host(whole), "%s cut=%d" % (mode, cut))
+
+
+def test_stochastic_distribution_matches_reference_counts(F, golden_dir):
+    """Tolerance: |p_hat - p_ref| <= 5 * sqrt(2 p(1-p)/N) with N = 2^18 draws per probe value (the fixture holds
+    the reference CPU op's observed counts); the two possible outputs must be exactly the reference's."""
+    g = np.load(os.path.join(golden_dir, "stochastic.npz"))
+    N = int(g["N"][0])
+    for key in g.files:
+        if key == "N":
+            continue
+        mode, v = key.split("@")
+        ref_vals, ref_cnt = g[key][0].astype(np.uint32), g[key][1].astype(np.float64)
+        x = torch.full((N,), float(v), dtype=torch.float32, device="cuda")
+        got = host(F.cast(x, mode, seed=4242, unscale_fp32=True))
+        u, c = np.unique(got.view(np.uint32), return_counts=True)
+        assert set(u.tolist()) == set(ref_vals.tolist()), key
+        for val, cnt in zip(u, c):
+            p_ref = ref_cnt[list(ref_vals).index(val)] / N
+            sigma = np.sqrt(max(p_ref * (1 - p_ref), 1e-9) / N)
+            assert abs(cnt / N - p_ref) <= 5 * np.sqrt(2) * sigma, (key, cnt / N, p_ref)
+
+
+def test_stochastic_is_unbiased_on_a_large_tensor(F):
+    """E[q - x] = 0 for in-range values: |mean(q - x)| <= 5 sigma / sqrt(n), n = 16 Mi N(0,1) samples."""
+    torch.manual_seed(0)
+    x = torch.randn(1 << 24, device="cuda")
+    for mode in ("E5M2_STOCHASTIC", "E4M3_STOCHASTIC", "E3M4_STOCHASTIC"):
+        q = F.cast(x, mode, seed=1)
+        keep = (x.abs() > 0.26) & (x.abs() < 16)                 # away from pseudo-subnormals / saturation
+        d = (q - x.half().float())[keep].double()                # rounding error w.r.t. the fp16 value being rounded
+        assert abs(d.mean().item()) <= 5 * d.std().item() / np.sqrt(d.numel()), mode
+
+
+# ------------------------------------------------------------------------------------------ amax / scale / rowwise
+@pytest.mark.parametrize("dt", [torch.float32, torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("n", [1, 5, 4096, 1000003])
+def test_amax(F, dt, n):
+    torch.manual_seed(n)
+    x = (torch.randn(n, device="cuda") * 37).to(dt)
+    if n > 3:
+        x[1] = float("nan")                                     # ignored, like fmaxf
+    got = F.amax(x).item()
+    want = x.float().abs().nan_to_num(nan=0.0).max().item()
+    assert got == want
+    off = F.amax(x[1:] if n > 1 else x).item()                  # unaligned view
+    assert off == (x[1:] if n > 1 else x).float().abs().nan_to_num(nan=0.0).max().item()
+
+
+def test_per_tensor_amax_scaled_cast_without_host_sync(F):
+    x = wide(1 << 18, seed=8)
+    x = x[np.isfinite(x)]
+    xt = dev(x)
+    y, d_scale = F.cast_amax_scaled(xt, "E4M3_RNE", return_scale=True)
+    s = O.scale_from_amax(O.amax(x), 448.0)
+    assert d_scale.item() == np.float32(s)
+    assert_same(host(y), O.cast(x, "E4M3_RNE", scale=s), "amax-scaled")
+    z = torch.zeros(1000, device="cuda")                         # amax 0 -> inf -> clamp to 6.55e4
+    _, d_scale = F.cast_amax_scaled(z, "E4M3_RNE", return_scale=True)
+    assert d_scale.item() == np.float32(6.55e4)
+
+
+@pytest.mark.parametrize("mode", ["E4M3_RNE", "E3M4_RNE", "E5M2_RNE", "E4M3_STOCHASTIC"])
+@pytest.mark.parametrize("shape", [(64, 147), (128, 576), (7, 4608), (1000, 16), (3, 5)])
+@pytest.mark.parametrize("dt", ["f32", "f16"])
+def test_rowwise_per_channel_cast(F, mode, shape, dt):
+    rng = np.random.default_rng(shape[0])
+    x = (rng.standard_normal(shape) * np.exp2(rng.integers(-4, 4, (shape[0], 1)))).astype(np.float32)
+    if dt == "f16":
+        x = x.astype(np.float16)
+    fmt = O.parse_mode(mode)[0]
+    flt_max = {0: 57344.0, 1: 448.0, 2: 30.0}[fmt]
+    got, scales = F.cast_rowwise(dev(x), mode, seed=5, return_scales=True)
+    want = np.empty_like(x)
+    for r in range(shape[0]):
+        s = O.scale_from_amax(O.amax(x[r]), flt_max)
+        assert scales[r].item() == np.float32(s)
+        want[r] = O.cast(x[r], mode, scale=s, seed=5, elem_offset=r * shape[1])
+    assert_same(host(got), want, "%s %s" % (mode, shape))
+
+
+@pytest.mark.parametrize("mode", ["E5M2_RNE", "E4M3_RNE", "E3M4_RNE", "E4M3_STOCHASTIC", "E4M3_IEEE_RNE", "FP4_NEAREST"])
+@pytest.mark.parametrize("bs", [8, 16, 32, 128, 256, 768, 1000, 4096])
+@pytest.mark.parametrize("dt", ["f32", "f16", "bf16"])
+def test_blocked_vs_oracle(F, mode, bs, dt):
+    rng = np.random.default_rng(bs)
+    n = bs * 24
+    x = (rng.standard_normal(n) * np.repeat(np.exp2(rng.integers(-6, 6, 24)), bs)).astype(np.float32)
+    x[:bs] = 0.0                                                 # an all-zero block gives NaN, as in the reference
+    xt = dev(x)
+    if dt == "f16":
+        xt = xt.half()
+    elif dt == "bf16":
+        xt = xt.bfloat16()
+    got = host(F.cast_blocked(xt, mode, bs, seed=6))
+    assert_same(got, O.cast_blocked(host(xt), mode, bs, seed=6), "%s bs=%d %s" % (mode, bs, dt))
+
+
+# ------------------------------------------------------------------------------------------ error behaviour
+def test_errors_are_exceptions_not_exit(F):
+    x = torch.ones(16, device="cuda")
+    with pytest.raises(ValueError):
+        F.cast(x, "E9M9_RNE")
+    with pytest.raises(ValueError):
+        F.cast(x, "E4M3_RNE", scale=70000.0)
+    with pytest.raises(RuntimeError):
+        F.cast(torch.ones(16), "E4M3_RNE")
+    with pytest.raises(RuntimeError):
+        F.cast(torch.ones(4, 4, device="cuda").t(), "E4M3_RNE")
+    with pytest.raises(TypeError):
+        F.cast(x.double(), "E4M3_RNE")
+    with pytest.raises(ValueError):
+        F.cast_blocked(x, "E4M3_RNE", 5)
