@@ -59,55 +59,74 @@ def committed_traffic(kernel_key):
 
 
 class ClockSampler(object):
-    """nvidia-smi clocks / throttle reasons sampled every 200 ms during the timed region."""
-    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    """SM clock and throttle reasons sampled through NVML every 20 ms during the timed region (a thread of this
+    process; the nvidia-smi CLI takes longer to start than a short timed region lasts)."""
 
     def __init__(self, index):
         self.index = index
-        self.proc = None
-        self.path = None
+        self.samples = []
+        self.reasons = set()
+        self.max_mhz = None
+        self._stop = False
+        self._thread = None
+        self._h = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self._nv = pynvml
+            uuid = None
+            try:
+                import torch
+                uuid = "GPU-" + str(torch.cuda.get_device_properties(index).uuid)
+            except Exception:
+                pass
+            self._h = None
+            if uuid is not None:
+                try:
+                    self._h = pynvml.nvmlDeviceGetHandleByUUID(uuid)
+                except Exception:
+                    self._h = None
+            if self._h is None:
+                self._h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self._h, pynvml.NVML_CLOCK_SM))
+        except Exception:
+            self._h = None
+
+    def _loop(self):
+        nv = self._nv
+        names = {"hw_slowdown": getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8),
+                 "hw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40),
+                 "sw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20),
+                 "sw_power_cap": getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4)}
+        get_reasons = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or \
+            getattr(nv, "nvmlDeviceGetCurrentClocksThrottleReasons", None)
+        while not self._stop:
+            try:
+                self.samples.append(float(nv.nvmlDeviceGetClockInfo(self._h, nv.NVML_CLOCK_SM)))
+                if get_reasons is not None:
+                    mask = int(get_reasons(self._h))
+                    for k, bit in names.items():
+                        if mask & bit:
+                            self.reasons.add(k)
+            except Exception:
+                pass
+            time.sleep(0.02)
 
     def start(self):
-        try:
-            fd, self.path = tempfile.mkstemp(suffix=".csv")
-            os.close(fd)
-            self.f = open(self.path, "w")
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "200"], stdout=self.f,
-                                         stderr=subprocess.DEVNULL)
-        except Exception:
-            self.proc = None
+        if self._h is None:
+            return
+        import threading
+        self._thread = threading.Thread(target=self._loop, daemon=True)
+        self._thread.start()
 
     def stop(self):
-        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
-        if self.proc is None:
-            return out
-        try:
-            self.proc.terminate()
-            self.proc.wait(timeout=5)
-            self.f.close()
-            sm, mx, reasons = [], [], set()
-            names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-            with open(self.path) as f:
-                for line in f:
-                    p = [c.strip() for c in line.split(",")]
-                    if len(p) < 7:
-                        continue
-                    try:
-                        sm.append(float(p[0])); mx.append(float(p[1]))
-                    except ValueError:
-                        continue
-                    for nm, val in zip(names, p[3:7]):
-                        if val.lower().startswith("active"):
-                            reasons.add(nm)
-            os.unlink(self.path)
-            if sm:
-                out = {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons),
-                       "samples": len(sm)}
-        except Exception:
-            pass
-        return out
+        if self._thread is None:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": [], "samples": 0}
+        self._stop = True
+        self._thread.join(timeout=2)
+        sm = self.samples
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(sm)}
 
 
 # ---------------------------------------------------------------------------------------------- reference arm

@@ -4,8 +4,8 @@
 // (mpemu/pytquant/cuda/fpemu_kernels.cu:1028-1381) for block_norm == false.
 //
 // Data movement: one 256-bit LDG + one 256-bit STG per thread per vector (8 fp32 / 16 half elements),
-// kUnroll vectors in flight per thread, warp-contiguous (thread t of a CTA touches vector base + t), grid
-// sized to a multiple of the SM count with a grid-stride loop.  No shared memory, no scratch memory.
+// 2 (fp32) or 4 (16-bit) vectors in flight per thread, warp-contiguous (thread t of a CTA touches vector
+// base + t), one pass per thread.  No shared memory, no scratch memory.
 // Algorithmic traffic: read 1 + write 1 element = 8 B/elem (fp32) or 4 B/elem (fp16 / bf16).
 #include "fpemu_cast_core.cuh"
 
@@ -26,21 +26,23 @@ __global__ void __launch_bounds__(kThreads) cast_vec_kernel(const CastArgs a) {
   const int64_t nvec = a.n / VE;
   const char* in = static_cast<const char*>(a.in);
   char* out = static_cast<char*>(a.out);
-  const int64_t stride = (int64_t)gridDim.x * (kThreads * kUnroll);
-  for (int64_t base = (int64_t)blockIdx.x * (kThreads * kUnroll) + threadIdx.x; base < nvec; base += stride) {
-    Vec32 v[kUnroll];
+  // One pass per thread, no grid-stride loop: on B200 a grid of ceil(nvec / (kThreads * U)) short-lived CTAs
+  // streams at ~6.9 TB/s while a persistent 148 x k grid of looping CTAs stays at 6.0-6.6 TB/s
+  // (profiles/tune_r1.txt) — the block scheduler overlaps one CTA's stores with the next one's loads.
+  constexpr int U = UnrollFor<DT>::value;
+  const int64_t base = (int64_t)blockIdx.x * (kThreads * U) + threadIdx.x;
+  Vec32 v[U];
 #pragma unroll
-    for (int j = 0; j < kUnroll; ++j) {
-      const int64_t vi = base + j * kThreads;
-      if (vi < nvec) v[j] = ldg256(in + vi * 32);
-    }
+  for (int j = 0; j < U; ++j) {
+    const int64_t vi = base + j * kThreads;
+    if (vi < nvec) v[j] = ldg256(in + vi * 32);
+  }
 #pragma unroll
-    for (int j = 0; j < kUnroll; ++j) {
-      const int64_t vi = base + j * kThreads;
-      if (vi < nvec) {
-        process_vec<FMT, RND, DAZ, DT, SCALED>(v[j], sc, a, a.elem_offset + (uint64_t)vi * VE);
-        stg256(out + vi * 32, v[j]);
-      }
+  for (int j = 0; j < U; ++j) {
+    const int64_t vi = base + j * kThreads;
+    if (vi < nvec) {
+      process_vec<FMT, RND, DAZ, DT, SCALED>(v[j], sc, a, a.elem_offset + (uint64_t)vi * VE);
+      stg256(out + vi * 32, v[j]);
     }
   }
   // ragged tail (< one vector): staged through a zero-padded register vector so it runs the same code
@@ -152,13 +154,13 @@ int launch_cast(const CastArgs& a, int dtype, cudaStream_t stream) {
   const int sms = device_info().sm_count;
   if (k != nullptr) {
     const int ve = dtype == FPEMU_DT_F32 ? 8 : 16;
+    const int u = dtype == FPEMU_DT_F32 ? UnrollFor<FPEMU_DT_F32>::value : UnrollFor<FPEMU_DT_F16>::value;
     const int64_t nvec = a.n / ve;
-    const int64_t per_cta = (int64_t)kThreads * kUnroll;
+    const int64_t per_cta = (int64_t)kThreads * u;
     int64_t want = (nvec + per_cta - 1) / per_cta;
-    if (want < 1) want = 1;
-    const int64_t cap = (int64_t)sms * FPEMU_CAST_CTAS_PER_SM;
-    const int grid = (int)(want < cap ? want : cap);
-    k<<<grid, kThreads, 0, stream>>>(a);
+    if (want < 1) want = 1;                                  // a launch with only the ragged tail
+    if (want > 0x7FFFFFFFLL) return FPEMU_ERR_TOO_LARGE;     // > 2^43 fp32 elements
+    k<<<(unsigned)want, kThreads, 0, stream>>>(a);
   } else {
     int64_t want = (a.n + 255) / 256;
     const int64_t cap = (int64_t)sms * 8;

@@ -17,13 +17,9 @@ struct CastArgs {
 };
 
 constexpr int kThreads = 256;
-#ifndef FPEMU_CAST_UNROLL
-#define FPEMU_CAST_UNROLL 2
-#endif
-constexpr int kUnroll = FPEMU_CAST_UNROLL;
-#ifndef FPEMU_CAST_CTAS_PER_SM
-#define FPEMU_CAST_CTAS_PER_SM 8
-#endif
+// 32-byte vectors in flight per thread (tuned on B200, profiles/tune_r1.txt): fp32 is HBM-bound with 2;
+// 16-bit tensors carry twice the elements per byte and want 4.
+template <int DT> struct UnrollFor { static constexpr int value = (DT == FPEMU_DT_F32) ? 2 : 4; };
 
 struct ScaleCtx { float scale, rscale; bool unscale32; };
 
@@ -63,7 +59,10 @@ __device__ __forceinline__ void process_vec(Vec32& v, const ScaleCtx& sc, const 
     for (int k = 0; k < kPairs; ++k) {
       uint32_t h;
       if (DT == FPEMU_DT_F16 && !SCALED) {
-        h = v.w[k];
+        // the reference multiplies by scale even when it is 1 (`in[gid] * scale`, fpemu_kernels.cu:420, 588),
+        // which turns every NaN encoding into the canonical 0x7FFF; HMUL2 by 1.0 does the same and is exact
+        // for everything else
+        h = as_u32(__hmul2(as_h2(v.w[k]), as_h2(0x3C003C00u)));
       } else {
         float2 f = get_pair<DT>(v, k);
         if (SCALED) { f.x *= sc.scale; f.y *= sc.scale; }

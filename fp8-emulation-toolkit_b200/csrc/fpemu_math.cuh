@@ -42,7 +42,6 @@ __device__ __forceinline__ float2 unpack_bf16x2(uint32_t b2) {
 
 // ------------------------------------------------------------------------------------------ Philox4x32-10
 // Counter-based generator (Salmon et al., SC'11).  key = 64-bit seed, counter = (ctr, 0, 0).
-struct PhiloxKeys { uint32_t k0[10], k1[10]; };
 
 __device__ __forceinline__ uint4 philox4x32_10(uint32_t seed_lo, uint32_t seed_hi, uint64_t ctr) {
   uint32_t c0 = (uint32_t)ctr, c1 = (uint32_t)(ctr >> 32), c2 = 0u, c3 = 0u;
@@ -258,7 +257,8 @@ __device__ __forceinline__ float cast_one(float x, int fmt, int rnd, int flags, 
   if (fmt == FPEMU_FMT_BF16) return __uint_as_float(round_one_bf16(__float_as_uint(x), rnd, rbits));
   if (fmt == FPEMU_FMT_FP16)
     return __half2float(__ushort_as_half((unsigned short)round_one_fp16(x, rnd, daz, input_is_half, rbits)));
-  if (fmt == FPEMU_FMT_FP4) return round_one_fp4(scaled ? scale * x : x) * (scaled ? rscale : 1.0f);
+  // FP4 always multiplies (`scale * in[gid]`, fpemu_kernels.cu:1005), which also canonicalises NaN inputs
+  if (fmt == FPEMU_FMT_FP4) return round_one_fp4((scaled ? scale : 1.0f) * x) * (scaled ? rscale : 1.0f);
   const uint32_t h = __half_as_ushort(__float2half_rn(scaled ? x * scale : x));
   const uint32_t q = round_one_h16(h, fmt, rnd, daz, rbits);
   float f = __half2float(__ushort_as_half((unsigned short)q));

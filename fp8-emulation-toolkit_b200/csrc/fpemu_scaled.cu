@@ -43,8 +43,9 @@ __global__ void __launch_bounds__(kAmaxThreads) amax_kernel(const void* in_, int
   const char* in = static_cast<const char*>(in_);
   const int64_t nvec = n / VE;
   float m = 0.0f;
-  const int64_t stride = (int64_t)gridDim.x * (kAmaxThreads * kAmaxUnroll);
-  for (int64_t base = (int64_t)blockIdx.x * (kAmaxThreads * kAmaxUnroll) + threadIdx.x; base < nvec; base += stride) {
+  {
+    // one pass per thread (same launch shape as the cast kernel)
+    const int64_t base = (int64_t)blockIdx.x * (kAmaxThreads * kAmaxUnroll) + threadIdx.x;
     Vec32 v[kAmaxUnroll];
 #pragma unroll
     for (int j = 0; j < kAmaxUnroll; ++j) {
@@ -68,7 +69,9 @@ __global__ void __launch_bounds__(kAmaxThreads) amax_kernel(const void* in_, int
   if (threadIdx.x < 32) {
     bits = threadIdx.x < kAmaxThreads / 32 ? warp_bits[threadIdx.x] : 0u;
     bits = warp_max_u32(bits);
-    if (threadIdx.x == 0 && bits != 0u) atomicMax(reinterpret_cast<unsigned int*>(d_amax), bits);
+    // most CTAs lose against the running maximum: look before paying for the atomic
+    if (threadIdx.x == 0 && bits > *reinterpret_cast<volatile unsigned int*>(d_amax))
+      atomicMax(reinterpret_cast<unsigned int*>(d_amax), bits);
   }
 }
 
@@ -313,8 +316,8 @@ extern "C" int fpemu_amax(const void* in, int64_t n, int dtype, float* d_amax, v
     const int64_t per_cta = (int64_t)kAmaxThreads * kAmaxUnroll;
     int64_t want = (n / ve + per_cta - 1) / per_cta;
     if (want < 1) want = 1;
-    const int64_t cap = (int64_t)sms * 8;
-    const int grid = (int)(want < cap ? want : cap);
+    if (want > 0x7FFFFFFFLL) return FPEMU_ERR_TOO_LARGE;
+    const unsigned grid = (unsigned)want;
     switch (dtype) {
       case FPEMU_DT_F32:  amax_kernel<FPEMU_DT_F32><<<grid, kAmaxThreads, 0, stream>>>(in, n, d_amax); break;
       case FPEMU_DT_F16:  amax_kernel<FPEMU_DT_F16><<<grid, kAmaxThreads, 0, stream>>>(in, n, d_amax); break;

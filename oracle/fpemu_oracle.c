@@ -352,7 +352,13 @@ static float round_fp4(float inval) {
 static float load_elem(const void* p, int64_t i, int dtype) {
   switch (dtype) {
     case FPEMU_DT_F32:  return ((const float*)p)[i];
-    case FPEMU_DT_F16:  return fpemu_oracle_half2float(((const uint16_t*)p)[i]);
+    case FPEMU_DT_F16: {
+      /* GPU half->float conversion returns the canonical NaN 0x7FFFFFFF for every NaN input (x86 keeps
+       * sign and payload); observable in the BFLOAT16 kernel, which masks instead of converting back. */
+      f32_t v; v.f = fpemu_oracle_half2float(((const uint16_t*)p)[i]);
+      if (!g_nan_mode && (v.u & 0x7FFFFFFFu) > 0x7F800000u) v.u = 0x7FFFFFFFu;
+      return v.f;
+    }
     default:            return bf16_to_float(((const uint16_t*)p)[i]);
   }
 }
@@ -363,6 +369,14 @@ static void store_elem(void* p, int64_t i, int dtype, float v) {
     case FPEMU_DT_F16:  ((uint16_t*)p)[i] = fpemu_oracle_float2half(v); break;
     default:            ((uint16_t*)p)[i] = float_to_bf16_rn(v); break;
   }
+}
+
+/* fp32 multiply as the GPU does it: a NaN result is the canonical 0x7FFFFFFF (sign and payload dropped);
+ * x86 propagates the operand's NaN.  Only observable where no float->half conversion follows (FP4). */
+static float mul_f32(float a, float b) {
+  f32_t r; r.f = a * b;
+  if (!g_nan_mode && (r.u & 0x7FFFFFFFu) > 0x7F800000u) r.u = 0x7FFFFFFFu;
+  return r.f;
 }
 
 static float recip_f32(float s) { return (float)(1.0 / (double)s); }  /* `float r = 1.0 / scale;` */
@@ -418,7 +432,7 @@ int fpemu_oracle_cast(const void* in, void* out, int64_t n, int dtype, int forma
                                                dtype == FPEMU_DT_F16, r));
         break;
       case FPEMU_FMT_FP4: {
-        float v = round_fp4(ks * x) * rs;
+        float v = mul_f32(round_fp4(mul_f32(ks, x)), rs);
         q = v;
         break;
       }
@@ -466,7 +480,7 @@ int fpemu_oracle_cast_blocked(const void* in, void* out, int64_t n, int64_t bloc
     for (int64_t i = b0; i < b0 + block_size; ++i) {
       float x = load_elem(in, i, dtype);
       uint32_t r = rnd ? rnd[i] : 0u;
-      float q = (format == FPEMU_FMT_FP4) ? round_fp4(scale * x) * rs
+      float q = (format == FPEMU_FMT_FP4) ? mul_f32(round_fp4(mul_f32(scale, x)), rs)
                                           : cast_one_h16(x, dtype, format, rounding, flags, scale, rs, r);
       store_elem(out, i, dtype, q);
     }

@@ -68,7 +68,8 @@ def wide(n=1 << 16, seed=11):
     x = rng.standard_normal(n).astype(np.float32) * np.exp2(rng.integers(-30, 20, n)).astype(np.float32)
     spec = np.array([0.0, -0.0, np.inf, -np.inf, np.nan, -np.nan, 1e-40, -1e-40, 65504, 65520, -65520, 3.4e38, 1e-45,
                      448, 464, 480, -448, 30, 31, -31, 57344, 61440, -61440], dtype=np.float32)
-    x[:len(spec)] = spec
+    k = min(n, len(spec))
+    x[:k] = spec[:k]
     return x
 
 

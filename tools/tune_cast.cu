@@ -1,0 +1,144 @@
+// tune_cast.cu — launch-shape sweep for the cast kernel (development tool, not part of the library).
+//   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -lineinfo -o tools/tune_cast tools/tune_cast.cu
+//   ./tools/tune_cast [log2_elems]
+#include <cstdio>
+#include <cstdlib>
+#include <functional>
+#include <algorithm>
+#include <vector>
+
+#include "../fp8-emulation-toolkit_b200/csrc/fpemu_cast_core.cuh"
+
+using namespace fpemu;
+namespace fpemu { const DeviceInfo& device_info() { static DeviceInfo d{148}; return d; } }
+
+#define CK(x) do { cudaError_t e = (x); if (e != cudaSuccess) { printf("CUDA error %s at %s:%d\n", cudaGetErrorString(e), __FILE__, __LINE__); exit(1); } } while (0)
+
+template <int FMT, int RND, int DT, bool SCALED, int THREADS, int UNROLL>
+__global__ void __launch_bounds__(THREADS) k_cast(const CastArgs a) {
+  constexpr int VE = DtInfo<DT>::kVecElems;
+  ScaleCtx sc; sc.scale = 1.f; sc.rscale = 1.f; sc.unscale32 = false;
+  if (SCALED) { sc.scale = a.scale; sc.rscale = __frcp_rn(a.scale); }
+  const int64_t nvec = a.n / VE;
+  const char* in = (const char*)a.in; char* out = (char*)a.out;
+  const int64_t stride = (int64_t)gridDim.x * (THREADS * UNROLL);
+  for (int64_t base = (int64_t)blockIdx.x * (THREADS * UNROLL) + threadIdx.x; base < nvec; base += stride) {
+    Vec32 v[UNROLL];
+#pragma unroll
+    for (int j = 0; j < UNROLL; ++j) { int64_t vi = base + j * THREADS; if (vi < nvec) v[j] = ldg256(in + vi * 32); }
+#pragma unroll
+    for (int j = 0; j < UNROLL; ++j) {
+      int64_t vi = base + j * THREADS;
+      if (vi < nvec) { process_vec<FMT, RND, false, DT, SCALED>(v[j], sc, a, a.elem_offset + (uint64_t)vi * VE); stg256(out + vi * 32, v[j]); }
+    }
+  }
+}
+
+// pure copies for the ceiling
+template <int THREADS, int UNROLL, int KIND>
+__global__ void __launch_bounds__(THREADS) k_copy(const char* in, char* out, int64_t nvec) {
+  const int64_t stride = (int64_t)gridDim.x * (THREADS * UNROLL);
+  for (int64_t base = (int64_t)blockIdx.x * (THREADS * UNROLL) + threadIdx.x; base < nvec; base += stride) {
+    Vec32 v[UNROLL];
+#pragma unroll
+    for (int j = 0; j < UNROLL; ++j) {
+      int64_t vi = base + j * THREADS;
+      if (vi < nvec) {
+        if (KIND == 0) v[j] = ldg256(in + vi * 32);
+        else if (KIND == 1) v[j] = *reinterpret_cast<const Vec32*>(in + vi * 32);
+        else asm volatile("ld.global.nc.L1::no_allocate.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(v[j].w[0]), "=r"(v[j].w[1]), "=r"(v[j].w[2]), "=r"(v[j].w[3]), "=r"(v[j].w[4]), "=r"(v[j].w[5]), "=r"(v[j].w[6]), "=r"(v[j].w[7]) : "l"(in + vi * 32));
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < UNROLL; ++j) {
+      int64_t vi = base + j * THREADS;
+      if (vi < nvec) {
+        if (KIND == 1) *reinterpret_cast<Vec32*>(out + vi * 32) = v[j];
+        else stg256(out + vi * 32, v[j]);
+      }
+    }
+  }
+}
+
+
+static float time_ms(int reps, const std::function<void()>& f) {
+  cudaEvent_t a, b; CK(cudaEventCreate(&a)); CK(cudaEventCreate(&b));
+  for (int i = 0; i < 3; ++i) f();
+  CK(cudaEventRecord(a));
+  for (int i = 0; i < reps; ++i) f();
+  CK(cudaEventRecord(b)); CK(cudaEventSynchronize(b));
+  float ms; CK(cudaEventElapsedTime(&ms, a, b));
+  CK(cudaGetLastError());
+  cudaEventDestroy(a); cudaEventDestroy(b);
+  return ms / reps;
+}
+
+template <int FMT, int RND, int DT, bool SCALED, int THREADS, int UNROLL>
+void run_cast(const char* name, const void* in, void* out, int64_t n, const std::vector<int>& cps) {
+  CastArgs a; a.in = in; a.out = out; a.n = n; a.scale = SCALED ? 3.7f : 1.f; a.d_scale = nullptr; a.seed_lo = 1; a.seed_hi = 2;
+  a.elem_offset = 0; a.fmt = FMT; a.rnd = RND; a.flags = 0;
+  const int ve = DtInfo<DT>::kVecElems; const double bytes = 2.0 * n * DtInfo<DT>::kBytes;
+  for (int c : cps) {
+    int64_t want = (n / ve + THREADS * UNROLL - 1) / (THREADS * UNROLL);
+    int grid = c > 0 ? (int)std::min<int64_t>(want, 148LL * c) : (int)want;
+    float ms = time_ms(10, [&] { k_cast<FMT, RND, DT, SCALED, THREADS, UNROLL><<<grid, THREADS>>>(a); });
+    printf("%-28s T=%4d U=%d ctas/sm=%3d grid=%8d  %8.4f ms  %7.1f GB/s\n", name, THREADS, UNROLL, c, grid, ms, bytes / ms / 1e6);
+  }
+}
+
+template <int THREADS, int UNROLL, int KIND>
+void run_copy(const char* name, const void* in, void* out, int64_t bytes_one, const std::vector<int>& cps) {
+  int64_t nvec = bytes_one / 32;
+  for (int c : cps) {
+    int64_t want = (nvec + THREADS * UNROLL - 1) / (THREADS * UNROLL);
+    int grid = c > 0 ? (int)std::min<int64_t>(want, 148LL * c) : (int)want;
+    float ms = time_ms(10, [&] { k_copy<THREADS, UNROLL, KIND><<<grid, THREADS>>>((const char*)in, (char*)out, nvec); });
+    printf("%-28s T=%4d U=%d ctas/sm=%3d grid=%8d  %8.4f ms  %7.1f GB/s\n", name, THREADS, UNROLL, c, grid, ms, 2.0 * bytes_one / ms / 1e6);
+  }
+}
+
+#define CASTS(FMT, RND, DT, SC, NAME) \
+  run_cast<FMT, RND, DT, SC, 256, 1>(NAME, in, out, n_for(DT), cps); \
+  run_cast<FMT, RND, DT, SC, 256, 2>(NAME, in, out, n_for(DT), cps); \
+  run_cast<FMT, RND, DT, SC, 256, 4>(NAME, in, out, n_for(DT), cps); \
+  run_cast<FMT, RND, DT, SC, 512, 2>(NAME, in, out, n_for(DT), cps); \
+  run_cast<FMT, RND, DT, SC, 128, 4>(NAME, in, out, n_for(DT), cps);
+
+int main(int argc, char** argv) {
+  int lg = argc > 1 ? atoi(argv[1]) : 30;
+  const int64_t n32 = 1LL << lg;
+  const int64_t bytes = n32 * 4;
+  void *in, *out;
+  CK(cudaMalloc(&in, bytes)); CK(cudaMalloc(&out, bytes));
+  // fill with a pattern of finite floats around 1.0 (N(0,1)-like exponents)
+  {
+    std::vector<uint32_t> h(1 << 20);
+    uint32_t s = 12345;
+    for (auto& w : h) { s = s * 1664525u + 1013904223u; uint32_t e = 120 + ((s >> 9) % 10); w = (s & 0x807FFFFFu) | (e << 23); }
+    for (int64_t off = 0; off < bytes; off += (int64_t)h.size() * 4) CK(cudaMemcpy((char*)in + off, h.data(), std::min<int64_t>(h.size() * 4, bytes - off), cudaMemcpyHostToDevice));
+  }
+  auto n_for = [&](int dt) { return dt == FPEMU_DT_F32 ? n32 : 2 * n32; };   // same bytes
+  std::vector<int> cps = {2, 4, 8, 16, 32, 0};
+  printf("# %lld MiB per buffer\n", (long long)(bytes >> 20));
+  float ms = time_ms(10, [&] { CK(cudaMemcpyAsync(out, in, bytes, cudaMemcpyDeviceToDevice)); });
+  printf("%-28s %8.4f ms  %7.1f GB/s\n", "cudaMemcpyAsync D2D", ms, 2.0 * bytes / ms / 1e6);
+  run_copy<256, 1, 0>("copy ld.na.256", in, out, bytes, cps);
+  run_copy<256, 2, 0>("copy ld.na.256", in, out, bytes, cps);
+  run_copy<256, 4, 0>("copy ld.na.256", in, out, bytes, cps);
+  run_copy<512, 2, 0>("copy ld.na.256", in, out, bytes, cps);
+  run_copy<256, 2, 1>("copy plain 256", in, out, bytes, cps);
+  run_copy<256, 2, 2>("copy ld.nc.na.256", in, out, bytes, cps);
+  CASTS(FPEMU_FMT_E5M2, FPEMU_RND_RTZ, FPEMU_DT_F32, false, "E5M2_RTZ f32")
+  CASTS(FPEMU_FMT_E5M2, FPEMU_RND_RNE, FPEMU_DT_F32, false, "E5M2_RNE f32")
+  CASTS(FPEMU_FMT_E4M3, FPEMU_RND_RNE, FPEMU_DT_F32, false, "E4M3_RNE f32")
+  CASTS(FPEMU_FMT_E4M3, FPEMU_RND_STOCHASTIC, FPEMU_DT_F32, false, "E4M3_SR f32")
+  CASTS(FPEMU_FMT_E4M3, FPEMU_RND_RNE, FPEMU_DT_F32, true, "E4M3_RNE f32 scaled")
+  CASTS(FPEMU_FMT_E3M4, FPEMU_RND_STOCHASTIC, FPEMU_DT_F32, false, "E3M4_SR f32")
+  CASTS(FPEMU_FMT_BF16, FPEMU_RND_RNE, FPEMU_DT_F32, false, "BF16_RNE f32")
+  CASTS(FPEMU_FMT_E4M3, FPEMU_RND_RNE, FPEMU_DT_BF16, false, "E4M3_RNE bf16")
+  CASTS(FPEMU_FMT_E4M3, FPEMU_RND_RNE, FPEMU_DT_BF16, true, "E4M3_RNE bf16 scaled")
+  CASTS(FPEMU_FMT_E4M3, FPEMU_RND_STOCHASTIC, FPEMU_DT_BF16, false, "E4M3_SR bf16")
+  CASTS(FPEMU_FMT_E4M3, FPEMU_RND_RNE, FPEMU_DT_F16, false, "E4M3_RNE f16")
+  return 0;
+}
