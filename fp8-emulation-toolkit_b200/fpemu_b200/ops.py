@@ -146,6 +146,29 @@ def cast_amax_scaled(x, mode, out=None, flt_max=None, seed=None, elem_offset=0, 
     return (y, d_scale) if return_scale else y
 
 
+def cast_amax_scaled_noalloc(x, mode, out, flt_max=None, seed=None, elem_offset=0, unscale_fp32=False):
+    """Per-tensor amax-scaled cast for callers that cannot allocate: `out` must be supplied (pass `x` for
+    in-place) and the library keeps the running maximum and the scale in its own static device array, so this
+    call allocates nothing on the device.  At most 512 MiB of input; calls sharing a GPU must not overlap
+    (see include/fpemu_b200.h).  Same numbers as `cast_amax_scaled`."""
+    _check_tensor(x)
+    _check_tensor(out, "out")
+    if out.dtype != x.dtype or out.numel() < x.numel():
+        raise ValueError("fpemu: out must match input dtype and size")
+    fmt, rnd, flags = L.parse_mode(mode)
+    if unscale_fp32:
+        flags |= L.FLAG_UNSCALE_FP32
+    if flt_max is None:
+        flt_max = FLT_MAX[fmt]
+    if rnd == L.RND_STOCHASTIC and seed is None:
+        seed = next_seed()
+    with _on_device(x):
+        st = L.lib().fpemu_cast_amax_scaled_noalloc(x.data_ptr(), out.data_ptr(), x.numel(), _dt(x), fmt, rnd, flags,
+                                                    float(flt_max), int(seed or 0), int(elem_offset), _stream(x))
+    L.check(st, "fpemu_cast_amax_scaled_noalloc(%s)" % mode)
+    return out
+
+
 def cast_rowwise(x2d, mode, out=None, flt_max=None, clamp=True, seed=None, elem_offset=0, unscale_fp32=False,
                  return_scales=False, rows=None, cols=None):
     """Per-channel (dim-0) amax-scaled cast in ONE launch (replaces the loop of qutils.py:289-311)."""

@@ -140,6 +140,26 @@ FPEMU_API int fpemu_cast_host(const void* h_in, void* h_out, int64_t n, int dtyp
                     int flags, float scale, uint64_t seed, void* d_stage0, void* d_stage1,
                     int64_t chunk_elems, void* stream_h2d, void* stream_compute, void* stream_d2h);
 
+/* Per-tensor amax-scaled cast that needs NO scratch memory from the caller and allocates none.
+ * (No counterpart in the reference: its Python layer computes the maximum with torch and passes a float.)
+ * Same result as fpemu_amax + fpemu_scale_from_amax + fpemu_cast with a device scalar, but the running
+ * maximum and the scale live in a 65 792-byte `static __device__` array inside the library, which every GPU
+ * that loads the library keeps until the process exits.  Meant for callers that cannot allocate device memory
+ * at all: a plugin inside a server whose pool was sized at start-up and belongs to the host framework, code
+ * that was handed its two buffers and owns no allocator, loops in which cudaMalloc is forbidden because it
+ * synchronises the device and can fail.  The caller still passes `in` and `out` (in == out allowed).
+ *   - Limit: at most 512 MiB of input per call (2^27 float32 or 2^28 float16/bfloat16 elements); more returns
+ *     FPEMU_ERR_TOO_LARGE and launches nothing.  BFLOAT16 / FLOAT16 targets take no scale: FPEMU_ERR_MODE.
+ *   - The first call on each device looks up the array's device address (cudaGetSymbolAddress); make that
+ *     first call before any stream capture starts.
+ *   - All calls on a GPU share the array.  Nothing needs clearing between calls (each call overwrites every
+ *     slot it later reads), but calls that overlap on the GPU race: keep them on one stream or order them with
+ *     events.
+ *   - Calls no cudaMalloc / cudaFree and no allocating library routine. */
+FPEMU_API int fpemu_cast_amax_scaled_noalloc(const void* in, void* out, int64_t n, int dtype, int format,
+                                             int rounding, int flags, float flt_max, uint64_t seed,
+                                             uint64_t elem_offset, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
