@@ -1,0 +1,81 @@
+"""Row-slab sharding of the cast across the GPUs of one node.
+
+Every element is independent, so a tensor of R rows is cut into contiguous row slabs, one per rank; the
+only exchange step is the per-tensor absolute maximum: each rank reduces its slabs into one float32 vector
+(one entry per tensor), ONE all-reduce(MAX) over that vector (NCCL over NVLink: 4*T bytes), then every rank
+derives the scales on its own device and casts its slabs.  `elem_offset` = the slab's first global element
+index keeps stochastic rounding identical for any world size.
+
+The kernel calls go through a small provider object so that the collective plumbing can be exercised with
+any tensor backend; the default provider is the CUDA library (there is no other implementation here)."""
+import torch
+import torch.distributed as dist
+
+from . import ops as _ops
+from . import _lib as L
+
+
+def slab_bounds(rows, world_size, rank):
+    """Rows [r0, r1) owned by `rank`: r0 = floor(rank * rows / world_size)."""
+    return (rank * rows) // world_size, ((rank + 1) * rows) // world_size
+
+
+class CudaKernels(object):
+    """Default kernel provider: the C ABI through fpemu_b200.ops."""
+    amax = staticmethod(_ops.amax)
+    scale_from_amax = staticmethod(_ops.scale_from_amax)
+    cast = staticmethod(_ops.cast)
+
+
+def _world(group):
+    if dist.is_available() and dist.is_initialized():
+        return dist.get_world_size(group), dist.get_rank(group)
+    return 1, 0
+
+
+def global_amax(slabs, group=None, kernels=CudaKernels, out=None):
+    """max|x| of each tensor over ALL ranks: local reductions into one vector, one all-reduce(MAX)."""
+    if not slabs:
+        return out
+    dev = slabs[0].device
+    vec = torch.zeros(len(slabs), dtype=torch.float32, device=dev) if out is None else out.zero_()
+    for t, x in enumerate(slabs):
+        if x.numel():
+            kernels.amax(x, out=vec[t:t + 1])
+    world, _ = _world(group)
+    if world > 1:
+        dist.all_reduce(vec, op=dist.ReduceOp.MAX, group=group)
+    return vec
+
+
+def sharded_amax_scaled_cast(slabs, mode, row_offsets=None, cols=None, outs=None, group=None, seed=0,
+                             flt_max=None, kernels=CudaKernels, unscale_fp32=False):
+    """Per-tensor amax-scaled cast of row-sharded tensors.
+
+    slabs        list of this rank's slabs (contiguous; slab t holds rows [row_offsets[t], ...) of tensor t)
+    row_offsets  first global row of each slab (default 0: unsharded); cols: row length of each tensor
+    outs         optional preallocated outputs (pass the slabs themselves for in-place)
+    Returns (outs, scales) where scales is the float32 device vector of per-tensor scales."""
+    fmt, _, _ = L.parse_mode(mode)
+    if flt_max is None:
+        flt_max = _ops.FLT_MAX[fmt]
+    n = len(slabs)
+    row_offsets = row_offsets or [0] * n
+    cols = cols or [(x.shape[-1] if x.dim() > 1 else 1) for x in slabs]
+    amax_vec = global_amax(slabs, group=group, kernels=kernels)
+    scales = kernels.scale_from_amax(amax_vec, flt_max)
+    results = []
+    for t, x in enumerate(slabs):
+        out = None if outs is None else outs[t]
+        results.append(kernels.cast(x, mode, out=out, d_scale=scales[t:t + 1], seed=seed + t,
+                                    elem_offset=row_offsets[t] * cols[t], unscale_fp32=unscale_fp32))
+    return results, scales
+
+
+def sharded_cast(slabs, mode, row_offsets=None, cols=None, outs=None, scale=1.0, seed=0, kernels=CudaKernels):
+    """Constant-scale cast of row-sharded tensors: no communication at all."""
+    n = len(slabs)
+    row_offsets = row_offsets or [0] * n
+    cols = cols or [(x.shape[-1] if x.dim() > 1 else 1) for x in slabs]
+    return [kernels.cast(x, mode, out=None if outs is None else outs[t], scale=scale, seed=seed + t,
+                         elem_offset=row_offsets[t] * cols[t]) for t, x in enumerate(slabs)]

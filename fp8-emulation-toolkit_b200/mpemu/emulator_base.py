@@ -1,0 +1,217 @@
+"""Shared machinery of the per-format emulators.
+
+The reference repeats this logic in every emulator class (e5m2_emu.py, e4m3_emu.py, e3m4_emu.py,
+hybrid_emu.py, bfloat16_emu.py); here it lives once and the subclasses only state their policy: which
+TensorQuantConfig each tensor role gets for training, calibration and inference."""
+import torch
+
+from .module_wrappers import AddMatmul, BatchMatmul, EltwiseAdd, EltwiseDiv, EltwiseMul, Matmul
+from .qutils import (ModuleQuantConfig, add_quantization_hooks, get_or_update_model_quant_config_dict,
+                     quantize_model_weights, reset_quantization_setup, set_quantize_weights_flag)
+from .scale_shift import replace_batchnorms_with_scaleshifts
+
+ROLES = ("emb", "wt", "iact", "oact", "igrad", "ograd", "wtgrad")
+
+
+class EmulatorBase(object):
+    tag = "emulator"
+    # "has_weight": drop weight configs of modules without a .weight (e5m2 / hybrid / bfloat16 emulators,
+    # e.g. hybrid_emu.py:262-265); "conv_linear": of everything but Conv2d / Linear (e4m3_emu.py:105-109)
+    weight_rule = "has_weight"
+
+    def __init__(self, model, optimizer, sparse_config=None, device="cuda", verbose=False, tensor_stats=False):
+        if sparse_config is not None:
+            raise NotImplementedError("sparsity is outside the fpemu cast path (DESIGN.md §7)")
+        self.whitelist = [torch.nn.Conv2d, torch.nn.Linear, torch.nn.Embedding, torch.nn.EmbeddingBag,
+                          Matmul, BatchMatmul, AddMatmul, EltwiseAdd, EltwiseMul, EltwiseDiv]
+        self.blacklist = []
+        self.list_unpatched = []
+        self.list_exempt_layers = None
+        self.list_layers_output_fused = None
+        self.using_apex = False
+        self.use_fp16_master = False
+        self.use_e5m2_master = False
+        self.use_e5m2_emb = self.use_e4m3_emb = self.use_e3m4_emb = False
+        self.emb_norm = False
+        self.device = device
+        self.model = model
+        self.global_steps = 0
+        self.is_training = model.training
+        self.patch_ops = False
+        self.patch_impl = "NONE"
+        self.sparse_config = None
+        self.data_emulation = True
+        self.mod_qconfig = None
+        self.model_qconfig_dict = None
+        self.hook_handles = None
+        self.verbose = verbose
+        self.tensor_stats = False
+        self.tb_writer = None
+        for role in ROLES:
+            setattr(self, role + "_qconfig", None)
+        self.set_training_qconfig()
+        if self.is_training and optimizer is not None and hasattr(optimizer, "_amp_stash"):
+            self.using_apex = True      # apex-amp optimizers carry fp32 master params (hybrid_emu.py:69-70)
+
+    # ---- policy (subclasses override)
+    def set_training_qconfig(self):
+        raise NotImplementedError
+
+    def set_calibration_qconfig(self):
+        self.set_default_inference_qconfig()
+
+    def set_default_inference_qconfig(self):
+        raise NotImplementedError
+
+    # ---- module selection
+    def blacklist_modules(self, list_modules):
+        for m in list_modules:
+            self.blacklist.append(m)
+            self.whitelist.remove(m)
+        self._rehook()
+
+    def whitelist_modules(self, list_modules):
+        for m in list_modules:
+            self.whitelist.append(m)
+            self.blacklist.remove(m)
+        self._rehook()
+
+    def _rehook(self):
+        if self.hook_handles is not None:
+            for h in self.hook_handles:
+                h.remove()
+        self.model_qconfig_dict = None
+        if self.mod_qconfig is not None:
+            self.create_or_update_hooks(self.model)
+
+    def create_or_update_hooks(self, model):
+        d = get_or_update_model_quant_config_dict(model, self.whitelist, self.mod_qconfig,
+                                                  model_qconfig_dict=self.model_qconfig_dict, override=True)
+        self.model_qconfig_dict = d
+        for name in (self.list_exempt_layers or []):
+            d.pop(name, None)
+        fused = self.list_layers_output_fused or []
+        for name, module in model.named_modules():
+            if name not in d:
+                continue
+            cfg = d[name]
+            if name in fused and type(module) in self.whitelist:
+                cfg.oact_qconfig = None
+                cfg.ograd_qconfig = None
+            if self.weight_rule == "conv_linear":
+                no_weight = type(module) not in (torch.nn.Conv2d, torch.nn.Linear)
+            else:
+                no_weight = not hasattr(module, "weight")
+            if no_weight:
+                cfg.wt_qconfig = None
+                cfg.wtgrad_qconfig = None
+            if type(module) in (torch.nn.Embedding, torch.nn.EmbeddingBag):
+                # embedding tables: only the table itself is cast (e4m3_emu.py:111-118)
+                cfg.wt_qconfig = self.emb_qconfig
+                cfg.iact_qconfig = cfg.igrad_qconfig = cfg.ograd_qconfig = cfg.oact_qconfig = None
+            if type(module) is BatchMatmul:
+                cfg.wt_qconfig = cfg.wtgrad_qconfig = cfg.oact_qconfig = cfg.ograd_qconfig = None
+        reset_quantization_setup(model, d)
+        self.hook_handles = add_quantization_hooks(model, d, is_training=self.is_training)
+        if not self.is_training:
+            # inference: quantize the weights once, then stop re-quantizing them every forward (e4m3_emu.py:133-136)
+            quantize_model_weights(model, d)
+            set_quantize_weights_flag(model, d, False)
+
+    def prepare_model(self, model, list_exempt_layers, list_layers_output_fused):
+        mq = ModuleQuantConfig(wt_qconfig=self.wt_qconfig, iact_qconfig=self.iact_qconfig,
+                               oact_qconfig=self.oact_qconfig, wtgrad_qconfig=self.wtgrad_qconfig,
+                               igrad_qconfig=self.igrad_qconfig, ograd_qconfig=self.ograd_qconfig,
+                               patch_ops=self.patch_ops)
+        mq.device = self.device
+        mq.patch_impl = self.patch_impl
+        self.mod_qconfig = mq
+        self.list_exempt_layers = list_exempt_layers
+        self.list_layers_output_fused = list_layers_output_fused
+        self.create_or_update_hooks(model)
+
+    def enable_hw_patching(self, patch_ops):
+        if patch_ops != "NONE":
+            raise RuntimeError("%s: HW patching uses the reference's CPU hardware model, which is out of scope here"
+                               % self.tag)
+
+    # ---- master parameters (hybrid_emu.py:110-232, e5m2_emu.py:111-232)
+    def set_master_param_precision(self, master_params):
+        if master_params in ("fp16", "FP16"):
+            self.use_fp16_master, self.use_e5m2_master = True, False
+        if master_params in ("e5m2", "BF8"):
+            self.use_e5m2_master, self.use_fp16_master = True, False
+
+    def set_embedding_precision(self, emb_precision, emb_norm=False):
+        if emb_precision in ("e5m2", "BF8"):
+            self.use_e5m2_emb = True
+        elif emb_precision in ("e4m3", "HF8"):
+            self.use_e4m3_emb = True
+        elif emb_precision in ("e4m3_2", "HF8_2"):
+            self.use_e3m4_emb = True
+        if emb_norm and (self.use_e5m2_emb or self.use_e4m3_emb or self.use_e3m4_emb):
+            self.emb_norm = emb_norm
+
+    def _master_params(self, optimizer):
+        if self.using_apex and hasattr(optimizer, "_master_params_to_model_params"):
+            from apex import amp
+            return list(amp.master_params(optimizer))
+        return None
+
+    def update_master_params(self, optimizer):
+        """Re-quantize the fp32 master copy after the optimizer step: FLOAT16_STOCHASTIC (or E5M2_STOCHASTIC)
+        in place, embeddings optionally to an fp8 format.  Only apex-amp optimizers keep master copies; without
+        them this prints a notice and does nothing, exactly like the reference (hybrid_emu.py:175-176)."""
+        masters = self._master_params(optimizer)
+        if masters is None:
+            if not getattr(self, "_warned_master", False):
+                print("%s: optimizer has no fp32 master parameters (apex amp O2); master-param emulation skipped" % self.tag)
+                self._warned_master = True
+            return
+        from .pytquant import fpemu_cuda
+        emb_mode = ("E5M2_STOCHASTIC" if self.use_e5m2_emb else "E4M3_STOCHASTIC" if self.use_e4m3_emb
+                    else "E3M4_STOCHASTIC" if self.use_e3m4_emb else None)
+        for param, (name, _) in zip(masters, self.model.named_parameters()):
+            if not param.is_cuda:
+                continue
+            if emb_mode is not None and "embeddings" in name:
+                param.data = fpemu_cuda.FPEmuOp.apply(param.data, "FLOAT16_STOCHASTIC", True)
+                if self.emb_norm:
+                    # the reference call passes (emb_norm, row_length) in the (scale, blocknorm) slots
+                    # (hybrid_emu.py:119); the intent — one block per embedding row — is what runs here
+                    param.data = fpemu_cuda.FPEmuOp.apply(param.data, emb_mode, True, 1.0, True, param.size()[1])
+                else:
+                    param.data = fpemu_cuda.FPEmuOp.apply(param.data, emb_mode, True)
+            elif self.use_fp16_master:
+                param.data = fpemu_cuda.FPEmuOp.apply(param.data, "FLOAT16_STOCHASTIC", True)
+            elif self.use_e5m2_master:
+                param.data = fpemu_cuda.FPEmuOp.apply(param.data, "E5M2_STOCHASTIC", True)
+
+    def optimizer_step(self, optimizer):
+        optimizer.step()
+        self.update_master_params(optimizer)
+        self.global_steps += 1
+
+    # ---- inference helpers
+    def fuse_layers_and_quantize_model(self, model):
+        if self.is_training:
+            print("Warning : emulator.is_training is set to True, returning the model unchanged")
+            return model
+        model = replace_batchnorms_with_scaleshifts(model)
+        self.set_default_inference_qconfig()
+        self.prepare_model(model, self.list_exempt_layers, self.list_layers_output_fused)
+        return model.to(self.device)
+
+    def enable_tensor_stats(self, summary_writer=None):
+        raise NotImplementedError("TensorBoard statistics are outside the fpemu cast path (DESIGN.md §7)")
+
+    def set_tensor_bindump_schedule(self, list_bindump_schedule):
+        raise NotImplementedError("tensor bin-dumps are outside the fpemu cast path (DESIGN.md §7)")
+
+    def print_config(self):
+        for key, cfg in (self.model_qconfig_dict or {}).items():
+            print("{} {:40s}".format(cfg, key))
+
+    def __repr__(self):
+        return "[Configured to run {} on {}, using AMP: {}]".format(
+            "training" if self.is_training else "inference", self.device, self.using_apex)

@@ -1,0 +1,378 @@
+"""qutils — tensor / module quantization configs, scale derivation and the module hooks.
+
+Same public names and call signatures as the reference's mpemu/qutils.py (cited per item), re-built around the
+device-side kernels:
+  * per-tensor `max` scaling: amax kernel -> scale kernel -> cast kernel, no host sync, no temporaries
+    (reference: abs() temp + max + `.item()`-style sync, qutils.py:282-287);
+  * per-channel scaling: ONE row-wise launch (reference: a Python loop of per-channel op calls, :289-311);
+  * fine-grained groups: one row-wise launch per tensor over (channel x group) rows (:313-337).
+Out of scope here: INT quantization (`quantize_to_integer`), tensor bin-dumps, TensorBoard stats,
+sparsity, op patching with the CPU hardware model.
+"""
+import copy
+from collections import OrderedDict
+
+import torch
+
+import fpemu_b200 as _F
+from fpemu_b200 import _lib as _L
+from .pytquant import fpemu_cuda
+
+# "fp16": un-scale through half like the reference CUDA op (default); "fp32": like the reference CPU op.
+_UNSCALE_FP32 = False
+
+
+def set_unscale_mode(mode):
+    """'fp16' (reference CUDA op semantics, default) or 'fp32' (reference CPU op semantics)."""
+    global _UNSCALE_FP32
+    if mode not in ("fp16", "fp32"):
+        raise ValueError("unscale mode must be 'fp16' or 'fp32'")
+    _UNSCALE_FP32 = (mode == "fp32")
+
+
+class TensorQuantConfig(object):
+    """Reference: TensorQuantConfig, mpemu/qutils.py:22-132 (same constructor, same attributes)."""
+    dtypes_all = ["e5m2", "e4m3", "e3m4", "fp4", "bfloat16", "float16"]
+    e5m2_modes = ["rtz", "stochastic", "rne", "rnaz", "rntz", "rpinf", "rninf",
+                  "daz_stochastic", "daz_rne", "daz_rnaz", "daz_rntz"]
+    e4m3_modes = ["rne", "stochastic"]
+    e4m3_ieee_modes = ["ieee_rne", "ieee_stochastic"]
+    e4m3_all_modes = e4m3_modes + e4m3_ieee_modes + ["rtz"]
+    e3m4_modes = ["rne", "stochastic", "rtz"]
+    fp4_modes = ["nearest"]
+    bfloat16_modes = ["rne", "stochastic", "rtz"]
+    float16_modes = ["rne", "stochastic", "daz_rne"]
+
+    def __init__(self, dtype=None, scheme=None, scaling="None", group_size=1):
+        self.dtype = dtype
+        self.scheme = scheme
+        parts = scaling.split("-")
+        self.scaling = "tensor" in parts
+        self.per_channel = "channel" in parts
+        self.scaling_method = "mean" if "mean" in parts else "max"
+        if "int" in self.dtype:
+            self.scaling_method = "none"
+        self.fine_grained = (scaling == "fine-grained")
+        self.group_size = group_size if self.fine_grained else 1
+        self.is_enabled = True
+        self.check_validity(dtype, scheme)
+
+    def check_validity(self, dtype, scheme):
+        if "int" in dtype:
+            return
+        assert dtype in self.dtypes_all, "Invalid data type {}, supported: {}".format(dtype, self.dtypes_all)
+        table = {"e5m2": self.e5m2_modes, "e4m3": self.e4m3_all_modes, "e3m4": self.e3m4_modes,
+                 "fp4": self.fp4_modes, "bfloat16": self.bfloat16_modes, "float16": self.float16_modes}
+        assert scheme in table[dtype], "scheme {} is not in {}".format(scheme, table[dtype])
+
+    def get_flt_max(self):
+        """Reference: qutils.py:100-114."""
+        if self.dtype == "e5m2":
+            return 57344.0
+        if self.dtype == "e4m3":
+            return 240.0 if self.scheme in self.e4m3_ieee_modes else 448.0
+        if self.dtype == "e3m4":
+            return 30.0
+        if self.dtype == "fp4":
+            return 1.0
+        return None
+
+    def get_flt_min(self):
+        """Reference: qutils.py:116-128."""
+        return {"e5m2": 1.5258789e-05, "e4m3": 1.9531250e-03, "e3m4": 1.5625000e-02,
+                "fp4": 0.000244140625}.get(self.dtype)
+
+    def mode_string(self):
+        mode = self.dtype.upper()
+        if self.scheme is not None:
+            mode += "_" + self.scheme.upper()
+        return mode
+
+    def __repr__(self):
+        how = ("per-channel" if self.per_channel else "per-tensor" if self.scaling
+               else "fine-grained" if self.fine_grained else "None")
+        return "[{}, scale: {}, method: {}]".format(self.dtype + "_" + str(self.scheme), how, self.scaling_method)
+
+
+class ModuleQuantConfig(object):
+    """Reference: ModuleQuantConfig, mpemu/qutils.py:137-198."""
+
+    def __init__(self, wt_qconfig=None, iact_qconfig=None, oact_qconfig=None,
+                 wtgrad_qconfig=None, igrad_qconfig=None, ograd_qconfig=None, patch_ops=False):
+        self.wt_qconfig = wt_qconfig
+        self.iact_qconfig = iact_qconfig
+        self.oact_qconfig = oact_qconfig
+        self.wtgrad_qconfig = wtgrad_qconfig
+        self.igrad_qconfig = igrad_qconfig
+        self.ograd_qconfig = ograd_qconfig
+        self.device = 'cuda'
+        self.patch_ops = patch_ops
+        self.patch_impl = "None"
+        self.sparse_config = None
+        self.global_step = -1
+        self.bin_dump = False
+        self.tensor_stats = False
+        self.tb_writer = None
+        self.weight_master = None
+
+    def register_output_grad_hook(self, output):
+        """Output-gradient tensor hook (reference :159-171): out-of-place cast of the incoming gradient."""
+        def quantize_output_grad(grad):
+            if self.ograd_qconfig is not None and self.ograd_qconfig.is_enabled:
+                grad = quantize_tensor(grad, self.ograd_qconfig, None, inplace=False)
+            return grad
+        if output.requires_grad:
+            output.register_hook(quantize_output_grad)
+
+    def register_weight_grad_hook(self, module):
+        """Weight-gradient tensor hook (reference :173-189): in-place cast."""
+        def quantize_weight_grad(grad):
+            if self.wtgrad_qconfig is not None and self.wtgrad_qconfig.is_enabled:
+                grad.data = quantize_tensor(grad.data, self.wtgrad_qconfig, None, inplace=True)
+            return grad
+        if type(module) in (torch.nn.Conv2d, torch.nn.Linear):
+            if module.weight is not None and module.weight.requires_grad:
+                module.weight.register_hook(quantize_weight_grad)
+
+    def __repr__(self):
+        if self.igrad_qconfig is None:
+            return "[weights: {}, inputs: {}, output: {}]".format(self.wt_qconfig, self.iact_qconfig, self.oact_qconfig)
+        return "[weights: {}, inputs: {}, output: {}, weight_grad: {}, input_grad: {}, output_grad: {}]".format(
+            self.wt_qconfig, self.iact_qconfig, self.oact_qconfig, self.wtgrad_qconfig, self.igrad_qconfig,
+            self.ograd_qconfig)
+
+
+class ModuleQuantParams(object):
+    """Reference: mpemu/qutils.py:204-214 (stateless formats carry no parameters)."""
+
+    def __init__(self, wt_qparams=None, iact_qparams=None, oact_qparams=None,
+                 wtgrad_qparams=None, igrad_qparams=None, ograd_qparams=None):
+        self.wt_qparams = wt_qparams
+        self.iact_qparams = iact_qparams
+        self.oact_qparams = oact_qparams
+        self.wtgrad_qparams = wtgrad_qparams
+        self.igrad_qparams = igrad_qparams
+        self.ograd_qparams = ograd_qparams
+
+
+def quantize_to_integer(tensor, mode, inplace=False):
+    raise NotImplementedError("INT quantization (reference qutils.py:216-247) is outside the fpemu cast path")
+
+
+def fpemu_device_fn(tensor, mode, inplace=True, scale=1.0):
+    """Reference: mpemu/qutils.py:249-261.  CUDA tensors only — there is no CPU op here."""
+    if "INT" in mode:
+        return quantize_to_integer(tensor, mode.split("_")[0], inplace=inplace)
+    if not tensor.is_cuda:
+        raise RuntimeError("fpemu: the B200 build has no CPU path; move the tensor to a CUDA device")
+    return fpemu_cuda.FPEmuOp.apply(tensor, mode, inplace, scale)
+
+
+def _mean_scale(mean, flt_min, floor):
+    """`mean` scaling (reference :276-281 / :294-301): scale = max(1, flt_min / mean) with a floor on the mean.
+    The reference divides a Python float by a float32 tensor, i.e. in float32 — so does this."""
+    import numpy as np
+    mean = abs(float(mean))
+    mean = mean if mean > floor else flt_min
+    scale = float(np.float32(flt_min) / np.float32(mean)) if mean > 0.0 else 1.0
+    return 1.0 if scale < 1.0 else scale
+
+
+class _ScaledCast(torch.autograd.Function):
+    """Device-side scaled casts with the same straight-through gradient as FPEmuOp."""
+
+    @staticmethod
+    def forward(ctx, tensor, mode, inplace, kind, flt_max, rows, cols, clamp):
+        src = tensor if tensor.is_contiguous() else tensor.contiguous()
+        out = src if (inplace and src is tensor) else torch.empty_like(src)
+        if kind == "tensor":
+            _F.cast_amax_scaled(src, mode, out=out, flt_max=flt_max, unscale_fp32=_UNSCALE_FP32)
+        else:
+            _F.cast_rowwise(src, mode, out=out, flt_max=flt_max, clamp=clamp, rows=rows, cols=cols,
+                            unscale_fp32=_UNSCALE_FP32)
+        if inplace:
+            if src is not tensor:
+                tensor.copy_(out)
+            ctx.mark_dirty(tensor)
+            return tensor
+        return out
+
+    @staticmethod
+    def backward(ctx, grad):
+        return grad, None, None, None, None, None, None, None
+
+
+def _supported_dtype(t):
+    return t.dtype in (torch.float32, torch.float16, torch.bfloat16)
+
+
+def quantize_tensor(tensor, qtconfig, qtparams, inplace=False):
+    """Single entry point for quantizing a tensor — reference: mpemu/qutils.py:264-345, same branches:
+    per-tensor (max / mean), per-channel over dim 0, fine-grained groups, unscaled."""
+    qtconfig.check_validity(qtconfig.dtype, qtconfig.scheme)
+    mode = qtconfig.mode_string()
+    if "INT" in mode:
+        return quantize_to_integer(tensor, mode.split("_")[0], inplace=inplace)
+    if not tensor.is_cuda:
+        raise RuntimeError("fpemu: the B200 build has no CPU path; move the tensor to a CUDA device")
+    fmt = _L.parse_mode(mode)[0]
+    takes_scale = fmt not in (_L.FMT_BF16, _L.FMT_FP16)
+    flt_max = qtconfig.get_flt_max()
+
+    if qtconfig.scaling is True:
+        if qtconfig.scaling_method == "mean":
+            mean = torch.mean(torch.abs(tensor.detach().flatten())).item()
+            scale = _mean_scale(mean, qtconfig.get_flt_min(), 1e-5)
+            return fpemu_device_fn(tensor, mode, inplace=inplace, scale=scale)
+        if takes_scale and _supported_dtype(tensor):
+            return _ScaledCast.apply(tensor, mode, inplace, "tensor", flt_max, 0, 0, True)
+        return fpemu_device_fn(tensor, mode, inplace=inplace)
+
+    if qtconfig.per_channel is True:
+        channels = tensor.shape[0]
+        cols = tensor.numel() // max(channels, 1)
+        if qtconfig.scaling_method == "mean":
+            # the reference takes the *mode* of each channel here (:297); rare path, kept in torch
+            out = tensor if inplace else torch.zeros_like(tensor)
+            for c in range(channels):
+                sub = tensor.select(0, c).detach()
+                m = abs(torch.mode(torch.flatten(sub)).values.item())
+                scale = _mean_scale(m, qtconfig.get_flt_min(), 1e-6)
+                out.select(0, c).data.copy_(fpemu_device_fn(sub, mode, inplace=False, scale=scale))
+            return out
+        if takes_scale and _supported_dtype(tensor):
+            return _ScaledCast.apply(tensor, mode, inplace, "rows", flt_max, channels, cols, True)
+        return fpemu_device_fn(tensor, mode, inplace=inplace)
+
+    if qtconfig.fine_grained is True:
+        # groups of `group_size` input channels inside every output channel (:313-337): with C divisible into
+        # equal chunks these are contiguous runs -> rows of a (K * chunks) x run matrix; no scale clamp here
+        k = tensor.shape[0]
+        in_ch = tensor.shape[1] if tensor.dim() > 1 else 1
+        chunks = max(1, int(in_ch / qtconfig.group_size))
+        if (qtconfig.scaling_method == "max" and takes_scale and _supported_dtype(tensor)
+                and tensor.dim() > 1 and in_ch % chunks == 0):
+            rows = k * chunks
+            return _ScaledCast.apply(tensor, mode, inplace, "rows", flt_max, rows, tensor.numel() // rows, False)
+        out = tensor if inplace else tensor.clone()
+        for kk in range(k):
+            crs = out.select(0, kk)
+            for sub in crs.chunk(chunks, 0):
+                if qtconfig.scaling_method == "mean":
+                    m = abs(torch.mode(torch.flatten(sub)).values.item())
+                    scale = _mean_scale(m, qtconfig.get_flt_min(), 1e-6)
+                else:
+                    scale = flt_max / torch.max(torch.abs(sub)).item()
+                sub.copy_(fpemu_device_fn(sub.contiguous(), mode, inplace=False, scale=scale))
+        return out
+
+    return fpemu_device_fn(tensor, mode, inplace=inplace)
+
+
+# --------------------------------------------------------------------------------------------- model plumbing
+def get_or_update_model_quant_config_dict(model, filter_module_types, mod_qconfig, prefix="",
+                                          model_qconfig_dict=None, override=False, exempt_modules=[]):
+    """Reference: mpemu/qutils.py:351-365."""
+    if model_qconfig_dict is None:
+        model_qconfig_dict = OrderedDict()
+    for name, module in model.named_modules():
+        fname = prefix + name
+        if type(module) in filter_module_types and fname not in exempt_modules:
+            if fname not in model_qconfig_dict or override:
+                model_qconfig_dict[fname] = copy.deepcopy(mod_qconfig)
+        elif type(module) not in filter_module_types and fname in model_qconfig_dict:
+            model_qconfig_dict.pop(fname)
+    return model_qconfig_dict
+
+
+def get_quantization_parameters(tensor, qtconfig):
+    return None       # stateless formats (reference :445-453)
+
+
+def quantize_weights_of_a_module(module, wt_qconfig, name=""):
+    """Reference: mpemu/qutils.py:458-468."""
+    module.weight.data.copy_(quantize_tensor(module.weight.data, wt_qconfig, None))
+
+
+def quantize_model_weights(model, model_qconfig_dict):
+    """Reference: mpemu/qutils.py:470-475."""
+    for name, module in model.named_modules():
+        if name in model_qconfig_dict and model_qconfig_dict[name].wt_qconfig is not None:
+            quantize_weights_of_a_module(module, model_qconfig_dict[name].wt_qconfig, name=name)
+
+
+def quantize_module_weights_and_inputs(self, input):
+    """Forward-pre hook (reference :478-549): weights in place, inputs out of place."""
+    qc = self.qconfig
+    if qc.wt_qconfig is not None and qc.wt_qconfig.dtype in ["bfloat16"]:
+        qc.weight_master = self.weight.data.clone()
+    if qc.wt_qconfig is not None and qc.wt_qconfig.is_enabled:
+        self.weight.data = quantize_tensor(self.weight.data, qc.wt_qconfig, self.qparams.wt_qparams, inplace=True)
+    if qc.iact_qconfig is not None and qc.iact_qconfig.is_enabled:
+        input = tuple(quantize_tensor(t, qc.iact_qconfig, None, inplace=False) if torch.is_tensor(t) and
+                      t.is_floating_point() else t for t in input)
+    return input
+
+
+def quantize_module_gradient(self, grad_input, grad_output):
+    """Full-backward hook (reference :551-584): input gradients out of place."""
+    qc = self.qconfig
+    if qc.igrad_qconfig is not None and qc.igrad_qconfig.is_enabled:
+        grad_input = tuple(quantize_tensor(g, qc.igrad_qconfig, self.qparams.igrad_qparams, inplace=False)
+                           if g is not None else None for g in grad_input)
+    if qc.wt_qconfig is not None and qc.wt_qconfig.dtype in ["bfloat16"] and qc.weight_master is not None:
+        self.weight.data = qc.weight_master.clone()
+    return grad_input
+
+
+def quantize_module_output(self, input, output):
+    """Forward hook (reference :586-616): register the output-gradient hook, cast the output in place."""
+    qc = self.qconfig
+    if torch.is_tensor(output):
+        qc.register_output_grad_hook(output)
+        if qc.oact_qconfig is not None and qc.oact_qconfig.is_enabled:
+            output = quantize_tensor(output, qc.oact_qconfig, self.qparams.oact_qparams, inplace=True)
+    return output
+
+
+def add_quantization_hooks(model, model_qconfig_dict, is_training=False):
+    """Reference: mpemu/qutils.py:618-633."""
+    handles = []
+    for name, module in model.named_modules():
+        if name in model_qconfig_dict:
+            handles.append(module.register_forward_pre_hook(quantize_module_weights_and_inputs))
+            handles.append(module.register_forward_hook(quantize_module_output))
+            if is_training:
+                if module.qconfig.igrad_qconfig is not None:
+                    handles.append(module.register_full_backward_hook(quantize_module_gradient))
+                module.qconfig.register_weight_grad_hook(module)
+    return handles
+
+
+def reset_quantization_setup(model, model_qconfig_dict):
+    """Reference: mpemu/qutils.py:636-642."""
+    for name, module in model.named_modules():
+        if name in model_qconfig_dict:
+            module.name = name
+            module.qconfig = copy.deepcopy(model_qconfig_dict[name])
+            module.qparams = ModuleQuantParams()
+
+
+def _set_flag(model, model_qconfig_dict, attr, value):
+    for name, module in model.named_modules():
+        if name in model_qconfig_dict:
+            cfg = getattr(module.qconfig, attr)
+            if cfg is not None:
+                cfg.is_enabled = value
+
+
+def set_quantize_weights_flag(model, model_qconfig_dict, set_value):
+    _set_flag(model, model_qconfig_dict, "wt_qconfig", set_value)        # reference :644-648
+
+
+def set_quantize_outputs_flag(model, model_qconfig_dict, set_value):
+    _set_flag(model, model_qconfig_dict, "oact_qconfig", set_value)      # reference :650-654
+
+
+def set_quantize_inputs_flag(model, model_qconfig_dict, set_value):
+    _set_flag(model, model_qconfig_dict, "iact_qconfig", set_value)      # reference :656-660
