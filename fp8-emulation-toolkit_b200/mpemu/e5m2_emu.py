@@ -5,6 +5,7 @@ from .qutils import TensorQuantConfig
 
 class E5M2Emulator(EmulatorBase):
     tag = "e5m2_emulator"
+    hooks_layernorm = True
 
     def set_training_qconfig(self):
         self.emb_qconfig = None

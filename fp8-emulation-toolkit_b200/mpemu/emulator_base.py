@@ -18,12 +18,17 @@ class EmulatorBase(object):
     # "has_weight": drop weight configs of modules without a .weight (e5m2 / hybrid / bfloat16 emulators,
     # e.g. hybrid_emu.py:262-265); "conv_linear": of everything but Conv2d / Linear (e4m3_emu.py:105-109)
     weight_rule = "has_weight"
+    # the e5m2 and hybrid emulators also hook LayerNorm (inputs / outputs / gradients are cast, its weight is not:
+    # e5m2_emu.py:28, :285-288; hybrid_emu.py:28, :283-286)
+    hooks_layernorm = False
 
     def __init__(self, model, optimizer, sparse_config=None, device="cuda", verbose=False, tensor_stats=False):
         if sparse_config is not None:
             raise NotImplementedError("sparsity is outside the fpemu cast path (DESIGN.md §7)")
         self.whitelist = [torch.nn.Conv2d, torch.nn.Linear, torch.nn.Embedding, torch.nn.EmbeddingBag,
                           Matmul, BatchMatmul, AddMatmul, EltwiseAdd, EltwiseMul, EltwiseDiv]
+        if self.hooks_layernorm:
+            self.whitelist.append(torch.nn.LayerNorm)
         self.blacklist = []
         self.list_unpatched = []
         self.list_exempt_layers = None
@@ -109,6 +114,8 @@ class EmulatorBase(object):
                 # embedding tables: only the table itself is cast (e4m3_emu.py:111-118)
                 cfg.wt_qconfig = self.emb_qconfig
                 cfg.iact_qconfig = cfg.igrad_qconfig = cfg.ograd_qconfig = cfg.oact_qconfig = None
+            if type(module) is torch.nn.LayerNorm:
+                cfg.wt_qconfig = None
             if type(module) is BatchMatmul:
                 cfg.wt_qconfig = cfg.wtgrad_qconfig = cfg.oact_qconfig = cfg.ograd_qconfig = None
         reset_quantization_setup(model, d)

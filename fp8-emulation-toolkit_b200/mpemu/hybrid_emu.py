@@ -1,13 +1,12 @@
 """HybridEmulator — forward tensors E4M3 RNE per-tensor, gradients E5M2 stochastic
 (reference: mpemu/hybrid_emu.py:24, defaults :56-61, calibration / inference :400-413)."""
-import torch
-
 from .emulator_base import EmulatorBase
 from .qutils import TensorQuantConfig
 
 
 class HybridEmulator(EmulatorBase):
     tag = "hybrid_emulator"
+    hooks_layernorm = True
 
     def __init__(self, model, optimizer, sparse_config=None, device="cuda", verbose=False, tensor_stats=False):
         super().__init__(model, optimizer, sparse_config, device=device, verbose=verbose, tensor_stats=tensor_stats)
@@ -30,9 +29,3 @@ class HybridEmulator(EmulatorBase):
         self.wt_qconfig = TensorQuantConfig("e3m4", "rne", "per-channel")
         self.iact_qconfig = TensorQuantConfig("e4m3", "rne", "per-tensor")
         self.oact_qconfig = self.igrad_qconfig = self.ograd_qconfig = self.wtgrad_qconfig = None
-
-    def create_or_update_hooks(self, model):
-        super().create_or_update_hooks(model)
-        for name, module in model.named_modules():     # LayerNorm weights stay untouched (hybrid_emu.py:283-286)
-            if type(module) is torch.nn.LayerNorm and name in self.model_qconfig_dict:
-                module.qconfig.wt_qconfig = None

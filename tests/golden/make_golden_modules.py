@@ -22,7 +22,10 @@ sys.path.insert(0, HERE)
 from oracle import ref_loader  # noqa: E402
 import models  # noqa: E402
 
-sys.modules["fpemu_cpp"] = ref_loader.load("fpemu_cpp_ref_scalar")
+# the build a real install of the reference produces on this host: setup.py compiles with -march=native, i.e. the
+# AVX-512 paths (the scalar bf16 path mis-rounds, cpp/fpemu_impl.cpp:321-324; RNE / stochastic modes used below are
+# the same in both builds for E5M2 / E4M3 / E3M4)
+sys.modules["fpemu_cpp"] = ref_loader.load("fpemu_cpp_ref_avx512") or ref_loader.load("fpemu_cpp_ref_scalar")
 for stub in ("simple_gemm_dev", "simple_conv2d_dev"):
     sys.modules[stub] = types.ModuleType(stub)
 sys.path.insert(0, os.environ.get("FPEMU_REFERENCE_ROOT", "/root/reference"))
@@ -85,6 +88,9 @@ try:
     rn, emu = ref_mpt.quantize_model(rn, dtype="e4m3", list_exempt_layers=["conv1", "bn1", "fc"], device="cpu")
     with torch.no_grad():
         out["rn50_e4m3_logits"] = rn(xr).numpy()
+        # noise floor of this randomly initialised network: the reference's own logits under a 1e-7 input perturbation
+        yp = rn(xr + 1e-7 * torch.randn(xr.shape, generator=torch.Generator().manual_seed(2))).numpy()
+    out["rn50_sensitivity"] = np.array([np.linalg.norm(yp - out["rn50_e4m3_logits"]) / np.linalg.norm(out["rn50_e4m3_logits"])])
     out["rn50_layer1_0_conv1_w"] = rn.layer1[0].conv1.weight.detach().numpy().copy()
     out["rn50_hooked_modules"] = np.array([len(emu.emulator.model_qconfig_dict)])
 except ImportError:
@@ -97,7 +103,13 @@ tgt = torch.randint(0, 4, (8,), generator=torch.Generator().manual_seed(4))
 out["mlp_ids"] = ids.numpy()
 out["mlp_tgt"] = tgt.numpy()
 m, emu = ref_mpt.initialize(m, None, training_algo="hybrid", list_exempt_layers=["head"], device="cpu")
+acts = {}
+for nm, mod in m.named_modules():
+    if nm:
+        mod.register_forward_hook(lambda mod_, inp, outp, nm=nm: acts.__setitem__(nm, outp.detach().clone()))
 logits = m(ids)
+for nm, v in acts.items():
+    out["mlp_act|" + nm] = v.numpy()
 loss = torch.nn.functional.cross_entropy(logits, tgt)
 loss.backward()
 out["mlp_logits"] = logits.detach().numpy()
