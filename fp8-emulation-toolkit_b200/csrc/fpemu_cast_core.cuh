@@ -85,28 +85,69 @@ __device__ __forceinline__ void process_vec(Vec32& v, const ScaleCtx& sc, const 
         put_pair<DT>(v, k, g);
       }
     }
-  } else {
-    // BFLOAT16 / FLOAT16 targets: per element on fp32 bits; 16 random bits per element,
-    // element g uses 16-bit lane (g % 8) of Philox(g / 8)
-    const bool daz = (a.flags & FPEMU_FLAG_DAZ) != 0;
+  } else if (FMT == FPEMU_FMT_BF16 && DT == FPEMU_DT_BF16) {
+    // a bf16 tensor cast to BFLOAT16: every rounding mode is the identity (stochastic bits are added below the
+    // kept bits and never carry); only the flush of exponent-field-0 values to +0 remains
 #pragma unroll
     for (int k = 0; k < kPairs; ++k) {
-      uint32_t rbits = 0u;
-      if (kSR) {
-        // pair k covers elements 2k, 2k+1 -> Philox call (2k / 8), lanes (2k % 8), (2k % 8) + 1 = one word
-        const uint4 r = philox4x32_10(a.seed_lo, a.seed_hi, (g0 >> 3) + (uint64_t)((2 * k) >> 3));
-        const int wsel = ((2 * k) & 7) >> 1;
-        rbits = wsel == 0 ? r.x : (wsel == 1 ? r.y : (wsel == 2 ? r.z : r.w));
-      }
-      float2 f = get_pair<DT>(v, k);
-      if (FMT == FPEMU_FMT_BF16) {
+      const uint32_t aabs = v.w[k] & kAbs2;
+      const uint32_t tiny = __hlt2_mask(*reinterpret_cast<const __nv_bfloat162*>(&aabs),
+                                        __float2bfloat162_rn(1.17549435e-38f));      // NaN lanes compare false
+      v.w[k] &= ~tiny;
+    }
+  } else if (FMT == FPEMU_FMT_BF16) {
+    // BFLOAT16 target from fp32 / fp16 tensors: packed path, element-wise redo only for vectors holding a NaN.
+    // 16 random bits per element: element g uses 16-bit lane (g % 8) of Philox(g / 8), i.e. pair k of the vector
+    // uses word ((2k) % 8) / 2 of call (2k) / 8.
+    const Vec32 orig = v;
+    uint32_t nan_any = 0u;
+    uint4 r0 = make_uint4(0u, 0u, 0u, 0u), r1 = r0;
+    if (kSR) {
+      r0 = philox4x32_10(a.seed_lo, a.seed_hi, g0 >> 3);
+      if (kPairs > 4) r1 = philox4x32_10(a.seed_lo, a.seed_hi, (g0 >> 3) + 1);
+    }
+    uint32_t packed[kPairs];
+#pragma unroll
+    for (int k = 0; k < kPairs; ++k) {
+      const uint4& rr = (k < 4) ? r0 : r1;
+      const int wsel = k & 3;
+      const uint32_t rbits = kSR ? (wsel == 0 ? rr.x : (wsel == 1 ? rr.y : (wsel == 2 ? rr.z : rr.w))) : 0u;
+      const float2 f = get_pair<DT>(v, k);
+      packed[k] = round_pair_bf16<RND>(f.x, f.y, rbits, nan_any);
+    }
+    if (nan_any == 0u) {
+#pragma unroll
+      for (int k = 0; k < kPairs; ++k) put_pair<DT>(v, k, unpack_bf16x2(packed[k]));
+    } else {
+      // rare: redo the vector element by element with the reference's integer rule (keeps NaN payload high bits)
+#pragma unroll
+      for (int k = 0; k < kPairs; ++k) {
+        const uint4& rr = (k < 4) ? r0 : r1;
+        const int wsel = k & 3;
+        const uint32_t rbits = kSR ? (wsel == 0 ? rr.x : (wsel == 1 ? rr.y : (wsel == 2 ? rr.z : rr.w))) : 0u;
+        float2 f = get_pair<DT>(orig, k);
         f.x = __uint_as_float(round_one_bf16(__float_as_uint(f.x), RND, rbits & 0xFFFFu));
         f.y = __uint_as_float(round_one_bf16(__float_as_uint(f.y), RND, rbits >> 16));
-      } else {
-        const bool ih = (DT == FPEMU_DT_F16);
-        f.x = __half2float(__ushort_as_half((unsigned short)round_one_fp16(f.x, RND, daz, ih, rbits & 0xFFFFu)));
-        f.y = __half2float(__ushort_as_half((unsigned short)round_one_fp16(f.y, RND, daz, ih, rbits >> 16)));
+        put_pair<DT>(v, k, f);
       }
+    }
+  } else {
+    // FLOAT16 target: per element; 13 random bits per element from the same 16-bit lanes as BFLOAT16
+    const bool daz = (a.flags & FPEMU_FLAG_DAZ) != 0;
+    uint4 r0 = make_uint4(0u, 0u, 0u, 0u), r1 = r0;
+    if (kSR) {
+      r0 = philox4x32_10(a.seed_lo, a.seed_hi, g0 >> 3);
+      if (kPairs > 4) r1 = philox4x32_10(a.seed_lo, a.seed_hi, (g0 >> 3) + 1);
+    }
+#pragma unroll
+    for (int k = 0; k < kPairs; ++k) {
+      const uint4& rr = (k < 4) ? r0 : r1;
+      const int wsel = k & 3;
+      const uint32_t rbits = kSR ? (wsel == 0 ? rr.x : (wsel == 1 ? rr.y : (wsel == 2 ? rr.z : rr.w))) : 0u;
+      float2 f = get_pair<DT>(v, k);
+      const bool ih = (DT == FPEMU_DT_F16);
+      f.x = __half2float(__ushort_as_half((unsigned short)round_one_fp16(f.x, RND, daz, ih, rbits & 0xFFFFu)));
+      f.y = __half2float(__ushort_as_half((unsigned short)round_one_fp16(f.y, RND, daz, ih, rbits >> 16)));
       put_pair<DT>(v, k, f);
     }
   }

@@ -111,8 +111,22 @@ __device__ __forceinline__ uint32_t round_pair_e5m2(uint32_t h, uint32_t r2) {
   return (h + inc) & kKeep & ~is_sub;
 }
 
-// E4M3 (LSHIFT 7, SAT 0x5F00 = 448, FLUSH 0x1800 = 2^-9, grid exponents 9 -> thresholds 2^-6, 2^-7, 2^-8) and
-// E3M4 (LSHIFT 6, SAT 0x4F80 = 30,  FLUSH 0x2400 = 2^-6, thresholds 2^-2 .. 2^-5) share one shape.
+// min(|h|, c) per lane with the absolute value folded into the instruction (HMNMX2 R, |R|, c).
+// NaN lanes return c (min picks the non-NaN operand), Inf lanes too.
+__device__ __forceinline__ uint32_t abs_min_h2(uint32_t h, uint32_t c) {
+  uint32_t r;
+  asm("{.reg .b32 t; abs.f16x2 t, %1; min.f16x2 %0, t, %2;}" : "=r"(r) : "r"(h), "r"(c));
+  return r;
+}
+
+// E4M3 (LSHIFT 7, SAT 0x5F00 = 448, FLUSH 0x1800 = 2^-9, pseudo-subnormals below 2^-6) and
+// E3M4 (LSHIFT 6, SAT 0x4F80 = 30,  FLUSH 0x2400 = 2^-6, pseudo-subnormals below 2^-2) share one shape.
+//
+// The reference clears the low d = G - e mantissa bits of a value in binade e < G (G = 9 for E4M3, 13 for
+// E3M4) before rounding, i.e. truncates |h| to a multiple of 2^(G-25).  The per-lane bit mask 2^d - 1 is
+// produced without per-lane shifts: p = 2^d as an fp16 number is an integer subtraction on the exponent
+// field, max(p, 1) handles d <= 0, and 1024 + p has p sitting in its mantissa bits.  HADD2 and IMAD.HI run
+// on the FMA pipe; everything else here is the ALU pipe, which is what bounds the 16-bit tensor variants.
 template <int FMT, int RND>
 __device__ __forceinline__ uint32_t round_pair_e4m3_like(uint32_t h, uint32_t r2) {
   constexpr bool E4 = (FMT == FPEMU_FMT_E4M3);
@@ -120,35 +134,56 @@ __device__ __forceinline__ uint32_t round_pair_e4m3_like(uint32_t h, uint32_t r2
   constexpr uint32_t kFlush = E4 ? 0x18001800u : 0x24002400u;
   constexpr uint32_t kKeep = E4 ? 0xFF80FF80u : 0xFFC0FFC0u;
   constexpr uint32_t kHalfM1 = E4 ? 0x003F003Fu : 0x001F001Fu;
+  constexpr uint32_t kGridExp = E4 ? 0x60006000u : 0x70007000u;   // (15 + G) << 10
   constexpr int kL = E4 ? 7 : 6;
-  const uint32_t sign = h & kSign2;
-  // saturate: min(|h|, max) as fp16 numbers; NaN and Inf lanes become max (min returns the non-NaN operand)
-  uint32_t a = as_u32(__hmin2(as_h2(h & kAbs2), as_h2(kSat)));
-  const __half2 av = as_h2(a);
-  const uint32_t keep = __hge2_mask(av, as_h2(kFlush));     // lanes below the flush threshold -> signed zero
+  // saturate: NaN and Inf lanes become the format maximum
+  const uint32_t a = abs_min_h2(h, kSat);
+  const uint32_t keep = __hge2_mask(as_h2(a), as_h2(kFlush));     // lanes below the flush threshold -> signed zero
   uint32_t r;
   if (RND == FPEMU_RND_RTZ) {
-    r = a & kKeep;                                          // clearing <= 4 low bits first changes nothing
+    r = a;                                                        // clearing <= 4 low bits first changes nothing
   } else {
-    // truncate |h| to a multiple of 2^-16 (E4M3) / 2^-12 (E3M4): clear 1..3 (1..4) low bits by binade
-    uint32_t m;
-    if (E4) {
-      uint32_t l9 = __hlt2_mask(av, as_h2(h2c(0x2400)));    // < 2^-6 : clear >= 1 bit
-      uint32_t l8 = __hlt2_mask(av, as_h2(h2c(0x2000)));    // < 2^-7 : clear >= 2 bits
-      uint32_t l7 = __hlt2_mask(av, as_h2(h2c(0x1C00)));    // < 2^-8 : clear 3 bits
-      m = l9 & (0x00010001u | (l8 & (0x00020002u | (l7 & 0x00040004u))));
-    } else {
-      uint32_t l13 = __hlt2_mask(av, as_h2(h2c(0x3400)));   // < 2^-2
-      uint32_t l12 = __hlt2_mask(av, as_h2(h2c(0x3000)));   // < 2^-3
-      uint32_t l11 = __hlt2_mask(av, as_h2(h2c(0x2C00)));   // < 2^-4
-      uint32_t l10 = __hlt2_mask(av, as_h2(h2c(0x2800)));   // < 2^-5
-      m = l13 & (0x00010001u | (l12 & (0x00020002u | (l11 & (0x00040004u | (l10 & 0x00080008u))))));
-    }
-    uint32_t ac = a & ~m;
-    uint32_t inc = (RND == FPEMU_RND_RNE) ? (kHalfM1 + ((ac >> kL) & 0x00010001u)) : r2;
-    r = (ac + inc) & kKeep;                                 // a saturated lane has zero low bits: unchanged
+    const uint32_t pbits = kGridExp - (a & 0x7C007C00u);          // fp16 encoding of 2^(G - e), per lane
+    const __half2 p = __hmax2(as_h2(pbits), as_h2(0x3C003C00u));  // d <= 0 -> 1 -> empty mask
+    const uint32_t q = as_u32(__hadd2(p, as_h2(0x64006400u)));    // 1024 + 2^d: mantissa field = 2^d
+    const uint32_t ac = a & ~(q - 0x64016401u);                   // clear the low d bits
+    uint32_t inc;
+    if (RND == FPEMU_RND_RNE) inc = kHalfM1 + (__umulhi(ac, 1u << (32 - kL)) & 0x00010001u);   // + lsb (ties to even)
+    else inc = r2;
+    r = ac + inc;                                                 // a saturated lane has zero low bits: unchanged
   }
-  return sign | (r & keep);
+  return (h & kSign2) | (r & kKeep & keep);
+}
+
+__device__ __forceinline__ uint32_t bf16x2_nan_lanes(uint32_t r) {
+  const __nv_bfloat162 v = *reinterpret_cast<__nv_bfloat162*>(&r);
+  return __hneu2_mask(v, v);
+}
+
+// BFLOAT16 target, two fp32 inputs -> packed bf16x2 encoding (reference BFLOAT16_Kernel, :266-304).
+// FMUL.FTZ by 1.0 flushes fp32 denormals (the reference zeroes every input whose exponent field is 0),
+// F2FP.BF16 rounds to nearest even / PRMT truncates, and lanes that came out as -0 become +0 (`uf.u = 0`).
+// NaN inputs are NOT handled here (the multiply canonicalises them, the reference keeps the payload's high
+// half): NaN lanes are reported through `nan_lanes` and the caller re-does such vectors element by element.
+// `r2` holds the two 16-bit random fields for stochastic rounding.
+template <int RND>
+__device__ __forceinline__ uint32_t round_pair_bf16(float x0, float x1, uint32_t r2, uint32_t& nan_lanes) {
+  float y0, y1;
+  asm("mul.ftz.f32 %0, %1, 0f3F800000;" : "=f"(y0) : "f"(x0));
+  asm("mul.ftz.f32 %0, %1, 0f3F800000;" : "=f"(y1) : "f"(x1));
+  uint32_t r;
+  if (RND == FPEMU_RND_RNE) {
+    r = pack_bf16x2_rn(y0, y1);
+    nan_lanes |= bf16x2_nan_lanes(r);
+  } else {
+    const uint32_t u0 = __float_as_uint(y0), u1 = __float_as_uint(y1);
+    r = __byte_perm(u0, u1, 0x7632);                                            // high halves of both words
+    nan_lanes |= bf16x2_nan_lanes(r);                                           // before the random add can wrap a NaN
+    if (RND == FPEMU_RND_STOCHASTIC)                                            // Inf + bits stays Inf after the cut
+      r = __byte_perm(u0 + (r2 & 0xFFFFu), u1 + (r2 >> 16), 0x7632);
+  }
+  const uint32_t zero = __heq2_mask(*reinterpret_cast<__nv_bfloat162*>(&r), __float2bfloat162_rn(0.0f));
+  return r & ~zero;
 }
 
 template <int FMT, int RND, bool DAZ>
