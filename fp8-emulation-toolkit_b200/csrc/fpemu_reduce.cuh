@@ -1,0 +1,58 @@
+// fpemu_reduce.cuh — absolute-maximum and scale-derivation device helpers shared by the scaled kernels.
+#pragma once
+
+#include "fpemu_cast_core.cuh"
+
+namespace fpemu {
+
+// ------------------------------------------------------------------------------------------ amax
+// max |x| of one 32-byte vector as a non-negative float; NaN lanes are ignored (fmaxf / hmax2 semantics,
+// as the reference's absmax0, fpemu_kernels.cu:194-195).
+template <int DT>
+__device__ __forceinline__ float vec_absmax(const Vec32& v) {
+  if (DT == FPEMU_DT_F32) {
+    float m = 0.0f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) m = fmaxf(m, fabsf(__uint_as_float(v.w[i])));
+    return m;
+  } else if (DT == FPEMU_DT_F16) {
+    __half2 m = as_h2(0u);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) m = __hmax2(m, as_h2(v.w[i] & kAbs2));
+    return fmaxf(__low2float(m), __high2float(m));
+  } else {
+    uint32_t z = 0u;
+    __nv_bfloat162 m = *reinterpret_cast<__nv_bfloat162*>(&z);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      uint32_t a = v.w[i] & kAbs2;
+      m = __hmax2(m, *reinterpret_cast<__nv_bfloat162*>(&a));
+    }
+    return fmaxf(__low2float(m), __high2float(m));
+  }
+}
+
+__device__ __forceinline__ float scale_from_amax(float amax, float flt_max, bool clamp) {
+  float s = __fdiv_rn(flt_max, amax);                       // `scale = flt_max / vmax`
+  if (clamp && s > 3.275e4f) s = 6.55e4f;                   // `scale = 6.55e+04 if scale > 3.275e+04`
+  return s;
+}
+
+// Power-of-two block scale from the block maximum (fpemu_kernels.cu:409-413, 577-581, 909-911, 998).
+__device__ __forceinline__ float block_scale(float maxval, int fmt, int dt) {
+  const float p2 = __uint_as_float(__float_as_uint(maxval) & 0x7F800000u);
+  switch (fmt) {
+    case FPEMU_FMT_E5M2:
+      if (dt == FPEMU_DT_F16) {                              // `scalar_t scale` is a half in this instantiation
+        float s = __half2float(__float2half_rn(2.0f * p2));
+        return __half2float(__float2half_rn(s * (1.0f / 16384.0f)));
+      }
+      return (2.0f * p2) * (1.0f / 16384.0f);
+    case FPEMU_FMT_E4M3:
+    case FPEMU_FMT_E4M3_IEEE: return (2.0f * p2) * 0.125f;
+    case FPEMU_FMT_E3M4:      return 2.0f * p2;
+    default:                  return __fdiv_rn(1.0f, maxval);    // FP4: 1 / max
+  }
+}
+
+}  // namespace fpemu

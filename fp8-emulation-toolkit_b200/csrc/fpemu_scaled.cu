@@ -3,36 +3,9 @@
 //   fpemu_scale_from_amax  device-side `flt_max / amax` + clamp of mpemu/qutils.py:283-285
 //   fpemu_cast_blocked     per-block power-of-two scale ("block_norm", fpemu_kernels.cu:150-170 + :407-414 ...)
 //   fpemu_cast_rowwise     per-channel amax-scaled cast (replaces the Python loop of mpemu/qutils.py:289-311)
-#include "fpemu_cast_core.cuh"
+#include "fpemu_reduce.cuh"
 
 namespace fpemu {
-
-// ------------------------------------------------------------------------------------------ amax
-// max |x| of one 32-byte vector as a non-negative float; NaN lanes are ignored (fmaxf / hmax2 semantics,
-// as the reference's absmax0, fpemu_kernels.cu:194-195).
-template <int DT>
-__device__ __forceinline__ float vec_absmax(const Vec32& v) {
-  if (DT == FPEMU_DT_F32) {
-    float m = 0.0f;
-#pragma unroll
-    for (int i = 0; i < 8; ++i) m = fmaxf(m, fabsf(__uint_as_float(v.w[i])));
-    return m;
-  } else if (DT == FPEMU_DT_F16) {
-    __half2 m = as_h2(0u);
-#pragma unroll
-    for (int i = 0; i < 8; ++i) m = __hmax2(m, as_h2(v.w[i] & kAbs2));
-    return fmaxf(__low2float(m), __high2float(m));
-  } else {
-    uint32_t z = 0u;
-    __nv_bfloat162 m = *reinterpret_cast<__nv_bfloat162*>(&z);
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      uint32_t a = v.w[i] & kAbs2;
-      m = __hmax2(m, *reinterpret_cast<__nv_bfloat162*>(&a));
-    }
-    return fmaxf(__low2float(m), __high2float(m));
-  }
-}
 
 constexpr int kAmaxThreads = 256;
 constexpr int kAmaxUnroll = 4;
@@ -85,35 +58,12 @@ __global__ void __launch_bounds__(256) amax_generic_kernel(const void* in, int64
   if ((threadIdx.x & 31) == 0 && bits != 0u) atomicMax(reinterpret_cast<unsigned int*>(d_amax), bits);
 }
 
-__device__ __forceinline__ float scale_from_amax(float amax, float flt_max, bool clamp) {
-  float s = __fdiv_rn(flt_max, amax);                       // `scale = flt_max / vmax`
-  if (clamp && s > 3.275e4f) s = 6.55e4f;                   // `scale = 6.55e+04 if scale > 3.275e+04`
-  return s;
-}
-
 __global__ void scale_from_amax_kernel(const float* d_amax, int count, float flt_max, float* d_scale) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < count) d_scale[i] = scale_from_amax(d_amax[i], flt_max, true);
 }
 
 // ------------------------------------------------------------------------------------------ blocked
-// Power-of-two block scale from the block maximum (fpemu_kernels.cu:409-413, 577-581, 909-911, 998).
-__device__ __forceinline__ float block_scale(float maxval, int fmt, int dt) {
-  const float p2 = __uint_as_float(__float_as_uint(maxval) & 0x7F800000u);
-  switch (fmt) {
-    case FPEMU_FMT_E5M2:
-      if (dt == FPEMU_DT_F16) {                              // `scalar_t scale` is a half in this instantiation
-        float s = __half2float(__float2half_rn(2.0f * p2));
-        return __half2float(__float2half_rn(s * (1.0f / 16384.0f)));
-      }
-      return (2.0f * p2) * (1.0f / 16384.0f);
-    case FPEMU_FMT_E4M3:
-    case FPEMU_FMT_E4M3_IEEE: return (2.0f * p2) * 0.125f;
-    case FPEMU_FMT_E3M4:      return 2.0f * p2;
-    default:                  return __fdiv_rn(1.0f, maxval);    // FP4: 1 / max
-  }
-}
-
 // Fast path: a quantization block is `vpb` (power of two, <= 32) consecutive 32-byte vectors, i.e. it lives in
 // `vpb` adjacent lanes of one warp: xor-shuffle butterfly, everything stays in registers (8 B/elem fp32).
 template <int FMT, int RND, int DT>
@@ -124,10 +74,10 @@ __global__ void __launch_bounds__(kThreads) blocked_vec_kernel(const CastArgs a,
   char* out = static_cast<char*>(a.out);
   ScaleCtx sc;
   sc.unscale32 = (a.flags & FPEMU_FLAG_UNSCALE_FP32) != 0;
-  const int64_t stride = (int64_t)gridDim.x * kThreads;
-  // every lane of a warp runs the same number of iterations (shuffles need the full warp)
-  const int64_t nvec_pad = (nvec + 31) & ~(int64_t)31;
-  for (int64_t vi = (int64_t)blockIdx.x * kThreads + threadIdx.x; vi < nvec_pad; vi += stride) {
+  // one vector per thread, one pass (same launch shape as the plain cast); lanes past the end stay in the
+  // warp because the shuffles below need all 32 of them
+  {
+    const int64_t vi = (int64_t)blockIdx.x * kThreads + threadIdx.x;
     const bool live = vi < nvec;
     Vec32 v;
     if (live) v = ldg256(in + vi * 32);
@@ -288,6 +238,8 @@ static RowwiseKernel pick_rowwise(int fmt, int rnd, int dt) {
 }
 
 int validate_cast(int64_t n, int dtype, int format, int rounding, float scale, const void* in, const void* out);
+bool launch_group_reg(const CastArgs& a, int dtype, int64_t groups, int64_t vectors_per_group, int rule, float flt_max,
+                      float* d_scale_out, cudaStream_t stream, int* status);
 
 static CastArgs make_args(const void* in, void* out, int64_t n, int format, int rounding, int flags, uint64_t seed,
                           uint64_t elem_offset) {
@@ -353,13 +305,18 @@ extern "C" int fpemu_cast_blocked(const void* in, void* out, int64_t n, int64_t 
   const bool aligned = (((uintptr_t)in | (uintptr_t)out) & 31u) == 0;
   const bool rng_ok = (rounding != FPEMU_RND_STOCHASTIC) || ((elem_offset & 15u) == 0);
   const int64_t vpb = block_size / ve;
+  // blocks that do not fit the in-warp butterfly: one warp / one CTA per block, block held in registers
+  if (aligned && rng_ok && block_size % ve == 0 && !(vpb <= 32 && (vpb & (vpb - 1)) == 0)) {
+    int status = 0;
+    if (launch_group_reg(a, dtype, n / block_size, vpb, 2, 0.0f, nullptr, stream, &status)) return status;
+  }
   BlockedKernel k = nullptr;
   if (aligned && rng_ok && block_size % ve == 0 && vpb <= 32 && (vpb & (vpb - 1)) == 0)
     k = pick_blocked(format, rounding, dtype);
   if (k != nullptr) {
-    int64_t want = (n / ve + kThreads - 1) / kThreads;
-    const int64_t cap = (int64_t)sms * 16;
-    k<<<(int)(want < cap ? want : cap), kThreads, 0, stream>>>(a, (int)vpb);
+    const int64_t want = (n / ve + kThreads - 1) / kThreads;
+    if (want > 0x7FFFFFFFLL) return FPEMU_ERR_TOO_LARGE;
+    k<<<(unsigned)want, kThreads, 0, stream>>>(a, (int)vpb);
   } else {
     int64_t want = (n / block_size + 7) / 8;                 // 8 warps per CTA, one warp per block
     const int64_t cap = (int64_t)sms * 8;
@@ -384,6 +341,10 @@ extern "C" int fpemu_cast_rowwise(const void* in, void* out, int64_t rows, int64
   const int ve = dtype == FPEMU_DT_F32 ? 8 : 16;
   const bool aligned = (((uintptr_t)in | (uintptr_t)out) & 31u) == 0 && cols % ve == 0;
   const bool rng_ok = (rounding != FPEMU_RND_STOCHASTIC) || ((elem_offset & 15u) == 0 && cols % 16 == 0);
+  if (aligned && rng_ok && (flags & FPEMU_FLAG_DAZ) == 0) {
+    int status = 0;   // rows that fit in registers: single pass
+    if (launch_group_reg(a, dtype, rows, cols / ve, clamp ? 0 : 1, flt_max, d_row_scale, stream, &status)) return status;
+  }
   RowwiseKernel k = (aligned && rng_ok && (flags & FPEMU_FLAG_DAZ) == 0) ? pick_rowwise(format, rounding, dtype) : nullptr;
   int64_t want = (rows + 7) / 8;                             // 8 warps per CTA, one warp per row
   const int64_t cap = (int64_t)sms * 8;

@@ -40,7 +40,13 @@ def _check_tensor(t, name="input"):
         raise RuntimeError("%s must be contiguous" % name)              # CHECK_CONTIGUOUS, :24
 
 
+_raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+
+
 def _stream(t):
+    """cudaStream_t (as int) of torch's current stream on t's device."""
+    if _raw_stream is not None:
+        return _raw_stream(t.device.index if t.device.index is not None else torch.cuda.current_device())
     return torch.cuda.current_stream(t.device).cuda_stream
 
 
