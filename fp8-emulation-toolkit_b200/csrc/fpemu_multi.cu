@@ -1,0 +1,259 @@
+// fpemu_multi.cu — multi-tensor launches: ONE amax launch and ONE cast launch for a whole list of tensors
+// (a model's parameter list, a rank's row slabs).  The reference casts tensor by tensor from Python
+// (mpemu/qutils.py:470-475, hybrid_emu.py:110-139); at 16-45 M elements per tensor a B200 spends as long ramping
+// kernels up and down as streaming, and below ~1 M elements the launches themselves dominate.
+//
+// The caller describes the tensors once (fpemu_multi_table_build, host side), uploads the resulting table and
+// passes its device address to the launches.  CTA b of a launch finds its tensor by comparing b against the
+// per-tensor first-CTA indices in the table (one coalesced table read per CTA, one ballot), then runs the same
+// per-vector code as the single-tensor kernels.
+#include "fpemu_reduce.cuh"
+
+namespace fpemu {
+
+struct MtEntry {
+  const void* in;
+  void* out;
+  int64_t n;
+  uint64_t elem_offset;
+  uint32_t cta_cast;      // first CTA of this tensor in the cast launch
+  uint32_t cta_amax;      // first CTA of this tensor in the amax launch
+};
+struct MtHeader {
+  int32_t count;
+  int32_t dtype;
+  uint32_t total_cast;
+  uint32_t total_amax;
+};
+static_assert(sizeof(MtEntry) == 40, "table layout");
+static_assert(sizeof(MtHeader) == 16, "table layout");
+
+constexpr int kMtAmaxUnroll = 4;
+
+__device__ __forceinline__ const MtEntry* mt_entries(const void* table) {
+  return reinterpret_cast<const MtEntry*>(static_cast<const char*>(table) + sizeof(MtHeader));
+}
+
+// Index of the tensor that owns CTA `b`: the last entry whose first-CTA index is <= b.  All threads of the
+// CTA take part; `AMAX` selects which of the two CTA numberings is used.
+template <bool AMAX>
+__device__ __forceinline__ int mt_find(const void* table, int count, uint32_t b) {
+  __shared__ int s_idx;
+  const MtEntry* e = mt_entries(table);
+  for (int base = 0; base < count; base += blockDim.x) {
+    const int t = base + threadIdx.x;
+    if (t < count) {
+      const uint32_t first = AMAX ? e[t].cta_amax : e[t].cta_cast;
+      const uint32_t next = (t + 1 < count) ? (AMAX ? e[t + 1].cta_amax : e[t + 1].cta_cast) : 0xFFFFFFFFu;
+      if (first <= b && b < next) s_idx = t;           // exactly one thread of one round matches
+    }
+  }
+  __syncthreads();
+  return s_idx;
+}
+
+template <int FMT, int RND, int DT, bool SCALED>
+__global__ void __launch_bounds__(kThreads) cast_multi_kernel(const void* table, const int count, const CastArgs proto,
+                                                             const float* d_scales) {
+  constexpr int VE = DtInfo<DT>::kVecElems;
+  constexpr int U = UnrollFor<DT>::value;
+  const int t = mt_find<false>(table, count, blockIdx.x);
+  const MtEntry e = mt_entries(table)[t];
+  CastArgs a = proto;
+  a.in = e.in; a.out = e.out; a.n = e.n; a.elem_offset = e.elem_offset;
+  a.seed_lo = proto.seed_lo + (uint32_t)t;                       // tensor t uses seed + t
+  a.seed_hi = proto.seed_hi + (a.seed_lo < proto.seed_lo ? 1u : 0u);
+  ScaleCtx sc;
+  sc.scale = 1.0f; sc.rscale = 1.0f;
+  sc.unscale32 = (a.flags & FPEMU_FLAG_UNSCALE_FP32) != 0;
+  if (SCALED) {
+    const float s = effective_scale(__ldg(d_scales + t), DT);
+    sc.scale = s;
+    sc.rscale = __frcp_rn(s);
+  }
+  const int64_t nvec = a.n / VE;
+  const char* in = static_cast<const char*>(a.in);
+  char* out = static_cast<char*>(a.out);
+  const int64_t local_cta = (int64_t)(blockIdx.x - e.cta_cast);
+  const int64_t base = local_cta * (kThreads * U) + threadIdx.x;
+  Vec32 v[U];
+#pragma unroll
+  for (int j = 0; j < U; ++j) {
+    const int64_t vi = base + j * kThreads;
+    if (vi < nvec) v[j] = ldg256(in + vi * 32);
+  }
+#pragma unroll
+  for (int j = 0; j < U; ++j) {
+    const int64_t vi = base + j * kThreads;
+    if (vi < nvec) {
+      process_vec<FMT, RND, false, DT, SCALED>(v[j], sc, a, a.elem_offset + (uint64_t)vi * VE);
+      stg256(out + vi * 32, v[j]);
+    }
+  }
+  // ragged tail of this tensor: its last CTA, thread 0, through a zero-padded register vector
+  const int tail = (int)(a.n - nvec * VE);
+  const int64_t ctas_of_t = (nvec + kThreads * U - 1) / (kThreads * U);
+  if (tail > 0 && local_cta == (ctas_of_t > 0 ? ctas_of_t - 1 : 0) && threadIdx.x == 0) {
+    Vec32 w;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) w.w[i] = 0u;
+    const int64_t e0 = nvec * VE;
+    if (DT == FPEMU_DT_F32) {
+      const uint32_t* p = reinterpret_cast<const uint32_t*>(a.in) + e0;
+      for (int i = 0; i < tail; ++i) w.w[i] = p[i];
+    } else {
+      const unsigned short* p = reinterpret_cast<const unsigned short*>(a.in) + e0;
+      for (int i = 0; i < tail; ++i) w.w[i >> 1] |= (uint32_t)p[i] << ((i & 1) * 16);
+    }
+    process_vec<FMT, RND, false, DT, SCALED>(w, sc, a, a.elem_offset + (uint64_t)e0);
+    if (DT == FPEMU_DT_F32) {
+      uint32_t* p = reinterpret_cast<uint32_t*>(a.out) + e0;
+      for (int i = 0; i < tail; ++i) p[i] = w.w[i];
+    } else {
+      unsigned short* p = reinterpret_cast<unsigned short*>(a.out) + e0;
+      for (int i = 0; i < tail; ++i) p[i] = (unsigned short)(w.w[i >> 1] >> ((i & 1) * 16));
+    }
+  }
+}
+
+template <int DT>
+__global__ void __launch_bounds__(kThreads) amax_multi_kernel(const void* table, const int count, float* d_amax) {
+  constexpr int VE = DtInfo<DT>::kVecElems;
+  const int t = mt_find<true>(table, count, blockIdx.x);
+  const MtEntry e = mt_entries(table)[t];
+  const char* in = static_cast<const char*>(e.in);
+  const int64_t nvec = e.n / VE;
+  const int64_t local_cta = (int64_t)(blockIdx.x - e.cta_amax);
+  const int64_t base = local_cta * (kThreads * kMtAmaxUnroll) + threadIdx.x;
+  float m = 0.0f;
+  Vec32 v[kMtAmaxUnroll];
+#pragma unroll
+  for (int j = 0; j < kMtAmaxUnroll; ++j) {
+    const int64_t vi = base + j * kThreads;
+    if (vi < nvec) v[j] = ldg256(in + vi * 32);
+    else {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) v[j].w[i] = 0u;
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < kMtAmaxUnroll; ++j) m = fmaxf(m, vec_absmax<DT>(v[j]));
+  if (local_cta == 0 && threadIdx.x < (int)(e.n - nvec * VE))
+    m = fmaxf(m, fabsf(load_elem(e.in, nvec * VE + threadIdx.x, DT)));
+  uint32_t bits = warp_max_u32(__float_as_uint(m));
+  __shared__ uint32_t warp_bits[kThreads / 32];
+  if ((threadIdx.x & 31) == 0) warp_bits[threadIdx.x >> 5] = bits;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    bits = threadIdx.x < kThreads / 32 ? warp_bits[threadIdx.x] : 0u;
+    bits = warp_max_u32(bits);
+    unsigned int* dst = reinterpret_cast<unsigned int*>(d_amax + t);
+    if (threadIdx.x == 0 && bits > *reinterpret_cast<volatile unsigned int*>(dst)) atomicMax(dst, bits);
+  }
+}
+
+typedef void (*MultiCastKernel)(const void*, const int, const CastArgs, const float*);
+
+template <int FMT, int RND, int DT>
+static MultiCastKernel mpick_scaled(bool scaled) {
+  if (FMT == FPEMU_FMT_BF16 || FMT == FPEMU_FMT_FP16) return cast_multi_kernel<FMT, RND, DT, false>;
+  return scaled ? cast_multi_kernel<FMT, RND, DT, true> : cast_multi_kernel<FMT, RND, DT, false>;
+}
+template <int FMT, int RND>
+static MultiCastKernel mpick_dt(int dt, bool scaled) {
+  switch (dt) {
+    case FPEMU_DT_F32:  return mpick_scaled<FMT, RND, FPEMU_DT_F32>(scaled);
+    case FPEMU_DT_F16:  return mpick_scaled<FMT, RND, FPEMU_DT_F16>(scaled);
+    default:            return mpick_scaled<FMT, RND, FPEMU_DT_BF16>(scaled);
+  }
+}
+template <int FMT>
+static MultiCastKernel mpick_rnd(int rnd, int dt, bool scaled) {
+  switch (rnd) {
+    case FPEMU_RND_RNE:        return mpick_dt<FMT, FPEMU_RND_RNE>(dt, scaled);
+    case FPEMU_RND_RTZ:        return (FMT == FPEMU_FMT_FP16) ? nullptr : mpick_dt<FMT, FPEMU_RND_RTZ>(dt, scaled);
+    case FPEMU_RND_STOCHASTIC: return mpick_dt<FMT, FPEMU_RND_STOCHASTIC>(dt, scaled);
+    default:                   return nullptr;
+  }
+}
+
+}  // namespace fpemu
+
+using namespace fpemu;
+
+extern "C" int64_t fpemu_multi_table_bytes(int count) {
+  if (count < 0) return FPEMU_ERR_ARG;
+  return (int64_t)sizeof(MtHeader) + (int64_t)count * (int64_t)sizeof(MtEntry);
+}
+
+extern "C" int fpemu_multi_table_build(const fpemu_tensor_desc* descs, int count, int dtype, void* h_table) {
+  if (count <= 0 || descs == nullptr || h_table == nullptr) return FPEMU_ERR_ARG;
+  if (dtype < 0 || dtype >= FPEMU_DT_COUNT) return FPEMU_ERR_DTYPE;
+  const int ve = dtype == FPEMU_DT_F32 ? 8 : 16;
+  const int u = dtype == FPEMU_DT_F32 ? UnrollFor<FPEMU_DT_F32>::value : UnrollFor<FPEMU_DT_F16>::value;
+  MtHeader* h = static_cast<MtHeader*>(h_table);
+  MtEntry* e = reinterpret_cast<MtEntry*>(static_cast<char*>(h_table) + sizeof(MtHeader));
+  uint64_t cast_ctas = 0, amax_ctas = 0;
+  for (int t = 0; t < count; ++t) {
+    const fpemu_tensor_desc& d = descs[t];
+    if (d.n < 0 || (d.n > 0 && (d.in == nullptr || d.out == nullptr))) return FPEMU_ERR_ARG;
+    // the multi-tensor kernels only have the vector path: 32-byte aligned buffers, Philox-group aligned offsets
+    if ((((uintptr_t)d.in | (uintptr_t)d.out) & 31u) != 0 || (d.elem_offset & 15u) != 0) return FPEMU_ERR_ALIGN;
+    e[t].in = d.in; e[t].out = d.out; e[t].n = d.n; e[t].elem_offset = d.elem_offset;
+    e[t].cta_cast = (uint32_t)cast_ctas;
+    e[t].cta_amax = (uint32_t)amax_ctas;
+    const int64_t nvec = d.n / ve;
+    int64_t c = (nvec + (int64_t)kThreads * u - 1) / ((int64_t)kThreads * u);
+    int64_t m = (nvec + (int64_t)kThreads * kMtAmaxUnroll - 1) / ((int64_t)kThreads * kMtAmaxUnroll);
+    if (d.n > 0 && c == 0) c = 1;                                  // a tensor that is only a ragged tail
+    if (d.n > 0 && m == 0) m = 1;
+    cast_ctas += (uint64_t)c;
+    amax_ctas += (uint64_t)m;
+    if (cast_ctas > 0x7FFFFFFFull || amax_ctas > 0x7FFFFFFFull) return FPEMU_ERR_TOO_LARGE;
+  }
+  h->count = count; h->dtype = dtype; h->total_cast = (uint32_t)cast_ctas; h->total_amax = (uint32_t)amax_ctas;
+  return FPEMU_OK;
+}
+
+extern "C" int fpemu_amax_multi(const void* d_table, const void* h_table, int count, float* d_amax, void* stream_) {
+  if (d_table == nullptr || h_table == nullptr || d_amax == nullptr || count <= 0) return FPEMU_ERR_ARG;
+  const MtHeader* h = static_cast<const MtHeader*>(h_table);
+  if (h->count != count) return FPEMU_ERR_ARG;
+  if (h->total_amax == 0) return FPEMU_OK;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  switch (h->dtype) {
+    case FPEMU_DT_F32:  amax_multi_kernel<FPEMU_DT_F32><<<h->total_amax, kThreads, 0, stream>>>(d_table, count, d_amax); break;
+    case FPEMU_DT_F16:  amax_multi_kernel<FPEMU_DT_F16><<<h->total_amax, kThreads, 0, stream>>>(d_table, count, d_amax); break;
+    default:            amax_multi_kernel<FPEMU_DT_BF16><<<h->total_amax, kThreads, 0, stream>>>(d_table, count, d_amax); break;
+  }
+  return (int)cudaGetLastError();
+}
+
+extern "C" int fpemu_cast_multi(const void* d_table, const void* h_table, int count, int format, int rounding, int flags,
+                                const float* d_scales, uint64_t seed, void* stream_) {
+  if (d_table == nullptr || h_table == nullptr || count <= 0) return FPEMU_ERR_ARG;
+  const MtHeader* h = static_cast<const MtHeader*>(h_table);
+  if (h->count != count) return FPEMU_ERR_ARG;
+  if (format < 0 || format >= FPEMU_FMT_COUNT || rounding < 0 || rounding >= FPEMU_RND_COUNT) return FPEMU_ERR_MODE;
+  if (flags & FPEMU_FLAG_DAZ) return FPEMU_ERR_MODE;             // DAZ variants: use the per-tensor entry point
+  const bool scaled = d_scales != nullptr && format != FPEMU_FMT_BF16 && format != FPEMU_FMT_FP16;
+  MultiCastKernel k = nullptr;
+  switch (format) {
+    case FPEMU_FMT_E5M2: k = mpick_rnd<FPEMU_FMT_E5M2>(rounding, h->dtype, scaled); break;
+    case FPEMU_FMT_E4M3: k = mpick_rnd<FPEMU_FMT_E4M3>(rounding, h->dtype, scaled); break;
+    case FPEMU_FMT_E3M4: k = mpick_rnd<FPEMU_FMT_E3M4>(rounding, h->dtype, scaled); break;
+    case FPEMU_FMT_BF16: k = mpick_rnd<FPEMU_FMT_BF16>(rounding, h->dtype, false); break;
+    case FPEMU_FMT_FP16: k = mpick_rnd<FPEMU_FMT_FP16>(rounding, h->dtype, false); break;
+    default: break;
+  }
+  if (k == nullptr) return FPEMU_ERR_MODE;                       // rare modes: use the per-tensor entry point
+  if (h->total_cast == 0) return FPEMU_OK;
+  CastArgs proto;
+  proto.in = nullptr; proto.out = nullptr; proto.n = 0;
+  proto.scale = 1.0f; proto.d_scale = nullptr;
+  proto.seed_lo = (uint32_t)seed; proto.seed_hi = (uint32_t)(seed >> 32);
+  proto.elem_offset = 0;
+  proto.fmt = format; proto.rnd = rounding; proto.flags = flags;
+  k<<<h->total_cast, kThreads, 0, static_cast<cudaStream_t>(stream_)>>>(d_table, count, proto, d_scales);
+  return (int)cudaGetLastError();
+}

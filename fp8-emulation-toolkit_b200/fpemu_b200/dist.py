@@ -72,6 +72,32 @@ def sharded_amax_scaled_cast(slabs, mode, row_offsets=None, cols=None, outs=None
     return results, scales
 
 
+class ShardedPlan(object):
+    """The multi-tensor version of sharded_amax_scaled_cast: the slab list is described to the library once and
+    every sweep is then three launches (amax, scale, cast) plus ONE all-reduce(MAX) over the float32[T] vector,
+    instead of 2T + 1 launches.  This is what makes the whole-model sweep scale past a few GPUs, where the
+    per-tensor version becomes launch-bound (tools/llama7b_sweep.py)."""
+
+    def __init__(self, slabs, row_offsets=None, cols=None, outs=None, group=None):
+        n = len(slabs)
+        row_offsets = row_offsets or [0] * n
+        cols = cols or [(x.shape[-1] if x.dim() > 1 else 1) for x in slabs]
+        self.group = group
+        self.plan = _ops.MultiTensorPlan(slabs, outs, [r * c for r, c in zip(row_offsets, cols)])
+
+    def _allreduce(self, vec):
+        world, _ = _world(self.group)
+        if world > 1:
+            dist.all_reduce(vec, op=dist.ReduceOp.MAX, group=self.group)
+
+    def amax_scaled_cast(self, mode, seed=0, flt_max=None, unscale_fp32=False):
+        return self.plan.amax_scaled_cast(mode, flt_max=flt_max, seed=seed, reduce_fn=self._allreduce,
+                                          unscale_fp32=unscale_fp32)
+
+    def cast(self, mode, seed=0):
+        return self.plan.cast(mode, seed=seed)
+
+
 def sharded_cast(slabs, mode, row_offsets=None, cols=None, outs=None, scale=1.0, seed=0, kernels=CudaKernels):
     """Constant-scale cast of row-sharded tensors: no communication at all."""
     n = len(slabs)

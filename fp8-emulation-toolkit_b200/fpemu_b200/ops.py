@@ -202,6 +202,83 @@ def cast_rowwise(x2d, mode, out=None, flt_max=None, clamp=True, seed=None, elem_
     return (out, scales) if return_scales else out
 
 
+class MultiTensorPlan(object):
+    """A fixed list of CUDA tensors (same dtype, same device) that is reduced / cast with ONE launch each.
+
+    Build it once for a parameter list or a set of row slabs (the table holds raw pointers, so the tensors must
+    stay alive and must not be re-allocated), then call `amax`, `cast` or `amax_scaled_cast` as often as needed.
+    Raises ValueError when a tensor is not 32-byte aligned or an offset is not a multiple of 16 — use the
+    per-tensor functions for such lists."""
+
+    def __init__(self, ins, outs=None, elem_offsets=None):
+        import ctypes
+        ins = list(ins)
+        if not ins:
+            raise ValueError("fpemu: empty tensor list")
+        outs = ins if outs is None else list(outs)
+        offs = [0] * len(ins) if elem_offsets is None else [int(o) for o in elem_offsets]
+        dev, dt = ins[0].device, ins[0].dtype
+        for x, y in zip(ins, outs):
+            _check_tensor(x)
+            _check_tensor(y, "out")
+            if x.device != dev or x.dtype != dt or y.dtype != dt or y.numel() < x.numel():
+                raise ValueError("fpemu: multi-tensor lists must share device and dtype, outputs must match inputs")
+        self.ins, self.outs, self.count, self.device, self.dtype = ins, outs, len(ins), dev, dt
+
+        class Desc(ctypes.Structure):
+            _fields_ = [("inp", ctypes.c_void_p), ("out", ctypes.c_void_p), ("n", ctypes.c_int64),
+                        ("off", ctypes.c_uint64)]
+        descs = (Desc * self.count)()
+        for i, (x, y, o) in enumerate(zip(ins, outs, offs)):
+            descs[i].inp, descs[i].out, descs[i].n, descs[i].off = x.data_ptr(), y.data_ptr(), x.numel(), o
+        nbytes = int(L.lib().fpemu_multi_table_bytes(self.count))
+        self.h_table = torch.empty(nbytes, dtype=torch.uint8)
+        st = L.lib().fpemu_multi_table_build(ctypes.addressof(descs), self.count, _DT[dt], self.h_table.data_ptr())
+        L.check(st, "fpemu_multi_table_build")
+        self.d_table = self.h_table.to(dev)
+        self.elements = sum(x.numel() for x in ins)
+
+    def amax(self, out=None):
+        """float32[count] vector of max|tensor t| (max-accumulated into `out` when given), one launch."""
+        if out is None:
+            out = torch.zeros(self.count, dtype=torch.float32, device=self.device)
+        with _on_device(self.d_table):
+            st = L.lib().fpemu_amax_multi(self.d_table.data_ptr(), self.h_table.data_ptr(), self.count, out.data_ptr(),
+                                          _stream(self.d_table))
+        L.check(st, "fpemu_amax_multi")
+        return out
+
+    def cast(self, mode, d_scales=None, seed=None, unscale_fp32=False):
+        """Cast every tensor in one launch; tensor t uses d_scales[t] (None: scale 1) and seed + t."""
+        fmt, rnd, flags = L.parse_mode(mode)
+        if unscale_fp32:
+            flags |= L.FLAG_UNSCALE_FP32
+        if rnd == L.RND_STOCHASTIC and seed is None:
+            seed = next_seed()
+        sp = None
+        if d_scales is not None:
+            if not (d_scales.is_cuda and d_scales.dtype == torch.float32 and d_scales.numel() >= self.count):
+                raise ValueError("fpemu: d_scales must be a float32 CUDA vector with one entry per tensor")
+            sp = d_scales.data_ptr()
+        with _on_device(self.d_table):
+            st = L.lib().fpemu_cast_multi(self.d_table.data_ptr(), self.h_table.data_ptr(), self.count, fmt, rnd, flags,
+                                          sp, int(seed or 0), _stream(self.d_table))
+        L.check(st, "fpemu_cast_multi(%s)" % mode)
+        return self.outs
+
+    def amax_scaled_cast(self, mode, flt_max=None, seed=None, reduce_fn=None, unscale_fp32=False):
+        """Per-tensor amax-scaled cast of the whole list: amax launch -> [reduce_fn(amax_vec), e.g. an all-reduce]
+        -> scale launch -> cast launch.  Returns (outs, scales)."""
+        fmt, _, _ = L.parse_mode(mode)
+        if flt_max is None:
+            flt_max = FLT_MAX[fmt]
+        vec = self.amax()
+        if reduce_fn is not None:
+            reduce_fn(vec)
+        scales = scale_from_amax(vec, flt_max)
+        return self.cast(mode, d_scales=scales, seed=seed, unscale_fp32=unscale_fp32), scales
+
+
 class HostCaster(object):
     """Host-buffer cast (pinned in, pinned out) pipelined through two device staging buffers.
     Owns the staging buffers and three streams; `run` is what the end-to-end benchmark times."""

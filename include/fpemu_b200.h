@@ -140,6 +140,28 @@ FPEMU_API int fpemu_cast_host(const void* h_in, void* h_out, int64_t n, int dtyp
                     int flags, float scale, uint64_t seed, void* d_stage0, void* d_stage1,
                     int64_t chunk_elems, void* stream_h2d, void* stream_compute, void* stream_d2h);
 
+/* ---- multi-tensor launches: one amax launch and one cast launch for a whole list of tensors -----------------
+ * Replaces the reference's tensor-by-tensor Python loops (mpemu/qutils.py:470-475 quantize_model_weights,
+ * mpemu/hybrid_emu.py:110-139 master-parameter loop, and any per-parameter sweep of a weight set).
+ * Usage: fill fpemu_tensor_desc[count]; fpemu_multi_table_build() writes a table of fpemu_multi_table_bytes(count)
+ * bytes into HOST memory; copy that table to the device once (it stays valid while the buffers do) and pass both
+ * copies to the launches.  Buffers must be 32-byte aligned and elem_offset a multiple of 16 (FPEMU_ERR_ALIGN
+ * otherwise: fall back to the per-tensor entry points); all tensors share one element type. */
+typedef struct fpemu_tensor_desc {
+  const void* in;        /* device input                                         */
+  void* out;             /* device output (may equal in)                         */
+  int64_t n;             /* elements                                             */
+  uint64_t elem_offset;  /* global index of element 0 (stochastic rounding)      */
+} fpemu_tensor_desc;
+
+FPEMU_API int64_t fpemu_multi_table_bytes(int count);
+FPEMU_API int fpemu_multi_table_build(const fpemu_tensor_desc* descs, int count, int dtype, void* h_table);
+/* d_amax[t] = max(d_amax[t], max|tensor t|) for every t, one launch. */
+FPEMU_API int fpemu_amax_multi(const void* d_table, const void* h_table, int count, float* d_amax, void* stream);
+/* Cast every tensor in one launch; tensor t uses scale d_scales[t] (NULL: scale 1) and seed + t. */
+FPEMU_API int fpemu_cast_multi(const void* d_table, const void* h_table, int count, int format, int rounding,
+                               int flags, const float* d_scales, uint64_t seed, void* stream);
+
 /* Per-tensor amax-scaled cast that needs NO scratch memory from the caller and allocates none.
  * (No counterpart in the reference: its Python layer computes the maximum with torch and passes a float.)
  * Same result as fpemu_amax + fpemu_scale_from_amax + fpemu_cast with a device scalar, but the running

@@ -381,3 +381,41 @@ def test_errors_are_exceptions_not_exit(F):
         F.cast(x.double(), "E4M3_RNE")
     with pytest.raises(ValueError):
         F.cast_blocked(x, "E4M3_RNE", 5)
+
+
+# ------------------------------------------------------------------------------------------ multi-tensor launches
+@pytest.mark.parametrize("mode", ["E4M3_RNE", "E5M2_STOCHASTIC", "E3M4_RTZ", "BFLOAT16_RNE", "FLOAT16_STOCHASTIC"])
+@pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16, torch.float16])
+def test_multi_tensor_launch_equals_per_tensor_calls(F, mode, dt):
+    """One launch over a ragged list of tensors (sizes 0 .. 300 001, several CTAs per tensor and several tensors per
+    CTA-size) == the per-tensor entry point, bit for bit, including per-tensor seeds and element offsets."""
+    torch.manual_seed(1)
+    sizes = [1, 7, 16, 17, 4096, 0, 300001, 65536, 8, 123457, 32, 2049] + [1000 + 16 * i for i in range(300)]
+    xs = [(torch.randn(n, device="cuda") * (1 + (i % 5))).to(dt) for i, n in enumerate(sizes)]
+    offs = [16 * (i * 3) for i in range(len(xs))]
+    plan = F.MultiTensorPlan(xs, [torch.empty_like(x) for x in xs], offs)
+    scales = (torch.rand(len(xs), device="cuda") * 4 + 0.25)
+    outs = plan.cast(mode, d_scales=scales, seed=1234)
+    for t, (x, y) in enumerate(zip(xs, outs)):
+        want = F.cast(x, mode, d_scale=scales[t:t + 1], seed=1234 + t, elem_offset=offs[t])
+        assert_same(host(y), host(want), "%s tensor %d (n=%d)" % (mode, t, x.numel()))
+    outs = plan.cast(mode, seed=99)                                   # unscaled
+    for t in (0, 3, 6, 11, 200):
+        assert_same(host(outs[t]), host(F.cast(xs[t], mode, seed=99 + t, elem_offset=offs[t])), "unscaled %d" % t)
+    vec = plan.amax()
+    for t, x in enumerate(xs):
+        assert vec[t].item() == (x.float().abs().max().item() if x.numel() else 0.0)
+
+
+def test_multi_tensor_amax_scaled_cast_and_rejects_unaligned(F):
+    xs = [torch.randn(n, device="cuda") * 0.02 for n in (4096 * 11, 777, 1 << 20)]
+    plan = F.MultiTensorPlan(xs, [torch.empty_like(x) for x in xs])
+    outs, scales = plan.amax_scaled_cast("E4M3_RNE")
+    for x, y, s in zip(xs, outs, scales):
+        want, ws = F.cast_amax_scaled(x, "E4M3_RNE", return_scale=True)
+        assert ws.item() == s.item()
+        assert_same(host(y), host(want), "amax-scaled multi")
+    with pytest.raises(ValueError):
+        F.MultiTensorPlan([xs[0][1:]])                                # not 32-byte aligned
+    with pytest.raises(ValueError):
+        F.MultiTensorPlan([xs[0]], elem_offsets=[8])                  # not a Philox-group boundary

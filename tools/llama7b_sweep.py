@@ -45,6 +45,7 @@ def main():
     ap.add_argument("--dtype", default="bf16", choices=["bf16", "fp32", "fp16"])
     ap.add_argument("--reps", type=int, default=5)
     ap.add_argument("--mode", default="E4M3_RNE")
+    ap.add_argument("--multi", action="store_true", help="multi-tensor launches (3 launches per sweep instead of 583)")
     args = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -71,7 +72,11 @@ def main():
     outs = [torch.empty_like(s) for s in slabs]
     local_elems = sum(s.numel() for s in slabs)
 
+    plan = fd.ShardedPlan(slabs, row_offsets=offsets, cols=cols, outs=outs) if args.multi else None
+
     def run():
+        if plan is not None:
+            return plan.amax_scaled_cast(args.mode, seed=7)
         return fd.sharded_amax_scaled_cast(slabs, args.mode, row_offsets=offsets, cols=cols, outs=outs, seed=7)
 
     def barrier():
@@ -115,7 +120,7 @@ def main():
                           "tensors": len(shapes), "elements": total, "elements_per_rank": local_elems,
                           "ms_per_sweep_device": ms, "ms_per_sweep_wall": wall * 1e3,
                           "aggregate_GBps_algorithmic": gbs, "per_gpu_GBps": gbs / world,
-                          "allreduce_us": ar_us, "launches_per_rank": 2 * len(shapes) + 1,
+                          "allreduce_us": ar_us, "launches_per_rank": 3 if args.multi else 2 * len(shapes) + 1,
                           "scaling": "strong"}))
     if world > 1:
         dist.destroy_process_group()
