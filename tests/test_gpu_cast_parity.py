@@ -419,3 +419,39 @@ def test_multi_tensor_amax_scaled_cast_and_rejects_unaligned(F):
         F.MultiTensorPlan([xs[0][1:]])                                # not 32-byte aligned
     with pytest.raises(ValueError):
         F.MultiTensorPlan([xs[0]], elem_offsets=[8])                  # not a Philox-group boundary
+
+
+# ------------------------------------------------------------------------------------------ out-of-bounds guard
+# (compute-sanitizer is closed on this GPU pool, so writes past the end are caught with sentinel-filled guard zones)
+@pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
+def test_no_writes_outside_the_output_buffer(F, dt):
+    guard = 64
+    sent = 123.0
+    for n in (1, 5, 8, 9, 15, 16, 17, 255, 256, 257, 4095, 4097, 65537):
+        for off in (0, 1, 3, 8):
+            big = torch.full((guard + off + n + guard,), sent, dtype=dt, device="cuda")
+            out = big[guard + off: guard + off + n]
+            x = (torch.randn(n, device="cuda") * 3).to(dt)
+            for mode in ("E4M3_RNE", "E5M2_STOCHASTIC", "BFLOAT16_RNE"):
+                F.cast(x, mode, out=out, seed=1)
+                assert bool((big[:guard + off] == sent).all()) and bool((big[guard + off + n:] == sent).all()), (n, off, mode)
+            if n % 8 == 0:
+                F.cast_blocked(x, "E4M3_RNE", 8, out=out)
+                assert bool((big[:guard + off] == sent).all()) and bool((big[guard + off + n:] == sent).all()), (n, off, "blocked")
+            F.cast_rowwise(x.view(1, n), "E4M3_RNE", out=out.view(1, n))
+            F.cast_amax_scaled(x, "E3M4_RNE", out=out)
+            F.cast_amax_scaled_noalloc(x, "E4M3_RNE", out=out)
+            assert bool((big[:guard + off] == sent).all()) and bool((big[guard + off + n:] == sent).all()), (n, off, "scaled")
+    # multi-tensor: outputs packed back to back inside one guarded arena (32-byte aligned pieces)
+    sizes = [16, 48, 1000 * 16, 7 * 16, 33 * 16]
+    arena = torch.full((guard + sum(sizes) + guard,), sent, dtype=dt, device="cuda")
+    pos, outs = guard, []
+    for n in sizes:
+        outs.append(arena[pos: pos + n])
+        pos += n
+    xs = [(torch.randn(n, device="cuda")).to(dt) for n in sizes]
+    if all(o.data_ptr() % 32 == 0 for o in outs):
+        F.MultiTensorPlan(xs, outs).cast("E4M3_RNE")
+        assert bool((arena[:guard] == sent).all()) and bool((arena[pos:] == sent).all())
+        for x, o in zip(xs, outs):
+            assert_same(host(o), host(F.cast(x, "E4M3_RNE")), "arena piece")
