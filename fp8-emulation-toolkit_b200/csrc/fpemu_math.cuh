@@ -111,48 +111,51 @@ __device__ __forceinline__ uint32_t round_pair_e5m2(uint32_t h, uint32_t r2) {
   return (h + inc) & kKeep & ~is_sub;
 }
 
-// min(|h|, c) per lane with the absolute value folded into the instruction (HMNMX2 R, |R|, c).
-// NaN lanes return c (min picks the non-NaN operand), Inf lanes too.
-__device__ __forceinline__ uint32_t abs_min_h2(uint32_t h, uint32_t c) {
+// clamp(h, -c, +c) per lane: min first so that NaN lanes become +c (min / max return the non-NaN operand).
+__device__ __forceinline__ uint32_t clamp_h2(uint32_t h, uint32_t c) {
   uint32_t r;
-  asm("{.reg .b32 t; abs.f16x2 t, %1; min.f16x2 %0, t, %2;}" : "=r"(r) : "r"(h), "r"(c));
+  asm("{.reg .b32 t, n; min.f16x2 t, %1, %2; neg.f16x2 n, %2; max.f16x2 %0, t, n;}" : "=r"(r) : "r"(h), "r"(c));
   return r;
 }
 
-// E4M3 (LSHIFT 7, SAT 0x5F00 = 448, FLUSH 0x1800 = 2^-9, pseudo-subnormals below 2^-6) and
-// E3M4 (LSHIFT 6, SAT 0x4F80 = 30,  FLUSH 0x2400 = 2^-6, pseudo-subnormals below 2^-2) share one shape.
+// E4M3 (LSHIFT 7, SAT 0x5F00 = 448, FLUSH 2^-9, pseudo-subnormals below 2^-6) and
+// E3M4 (LSHIFT 6, SAT 0x4F80 = 30,  FLUSH 2^-6, pseudo-subnormals below 2^-2) share one shape.
 //
 // The reference clears the low d = G - e mantissa bits of a value in binade e < G (G = 9 for E4M3, 13 for
-// E3M4) before rounding, i.e. truncates |h| to a multiple of 2^(G-25).  The per-lane bit mask 2^d - 1 is
-// produced without per-lane shifts: p = 2^d as an fp16 number is an integer subtraction on the exponent
-// field, max(p, 1) handles d <= 0, and 1024 + p has p sitting in its mantissa bits.  HADD2 and IMAD.HI run
-// on the FMA pipe; everything else here is the ALU pipe, which is what bounds the 16-bit tensor variants.
+// E3M4) before rounding, i.e. truncates |h| to a multiple of 2^(G-25), and flushes binades e < G - 3 (E4M3) /
+// e < G - 4 (E3M4).  Both per-lane decisions are derived from p = 2^(G-e), which as an fp16 number is one
+// integer subtraction on the exponent field:
+//   mask   2^d - 1 = relu(p - 1), moved into integer bits by adding 1024 (HFMA2.RELU + HADD2, FMA pipe);
+//   flush  factor sat(B - p) in {0, 1} with B = 9 (E4M3: keep p <= 8) / 17 (E3M4: keep p <= 16), applied with a
+//          final HMUL2 so the sign of a flushed value survives (HFMA2.SAT + HMUL2, FMA pipe).
+// Everything works on the signed encoding (sign-magnitude: adding to the low bits never reaches bit 15), so no
+// abs / sign-merge is needed.  Per pair: 8 ALU-pipe + 5 FMA-pipe instructions for RNE; the ALU pipe is what
+// bounds the 16-bit tensor variants (profiles/).
 template <int FMT, int RND>
 __device__ __forceinline__ uint32_t round_pair_e4m3_like(uint32_t h, uint32_t r2) {
   constexpr bool E4 = (FMT == FPEMU_FMT_E4M3);
   constexpr uint32_t kSat = E4 ? 0x5F005F00u : 0x4F804F80u;
-  constexpr uint32_t kFlush = E4 ? 0x18001800u : 0x24002400u;
   constexpr uint32_t kKeep = E4 ? 0xFF80FF80u : 0xFFC0FFC0u;
   constexpr uint32_t kHalfM1 = E4 ? 0x003F003Fu : 0x001F001Fu;
   constexpr uint32_t kGridExp = E4 ? 0x60006000u : 0x70007000u;   // (15 + G) << 10
+  constexpr uint32_t kKeepBias = E4 ? 0x48804880u : 0x4C404C40u;  // 9.0 / 17.0
   constexpr int kL = E4 ? 7 : 6;
-  // saturate: NaN and Inf lanes become the format maximum
-  const uint32_t a = abs_min_h2(h, kSat);
-  const uint32_t keep = __hge2_mask(as_h2(a), as_h2(kFlush));     // lanes below the flush threshold -> signed zero
+  const uint32_t c = clamp_h2(h, kSat);                           // saturate; NaN and Inf lanes become the maximum
+  const __half2 p = as_h2(kGridExp - (c & 0x7C007C00u));          // 2^(G - e) per lane
+  const __half2 keepf = __hfma2_sat(p, as_h2(0xBC00BC00u), as_h2(kKeepBias));   // 1.0 keep, 0.0 flush
   uint32_t r;
   if (RND == FPEMU_RND_RTZ) {
-    r = a;                                                        // clearing <= 4 low bits first changes nothing
+    r = c & kKeep;                                                // clearing <= 4 low bits first changes nothing
   } else {
-    const uint32_t pbits = kGridExp - (a & 0x7C007C00u);          // fp16 encoding of 2^(G - e), per lane
-    const __half2 p = __hmax2(as_h2(pbits), as_h2(0x3C003C00u));  // d <= 0 -> 1 -> empty mask
-    const uint32_t q = as_u32(__hadd2(p, as_h2(0x64006400u)));    // 1024 + 2^d: mantissa field = 2^d
-    const uint32_t ac = a & ~(q - 0x64016401u);                   // clear the low d bits
+    const __half2 m = __hfma2_relu(p, as_h2(0x3C003C00u), as_h2(0xBC00BC00u));  // 2^d - 1 (0 when d <= 0)
+    const uint32_t q = as_u32(__hadd2(m, as_h2(0x64006400u)));    // 1024 + (2^d - 1): the mask sits in the mantissa
+    const uint32_t ac = c & ~(q ^ 0x64006400u);                   // clear the low d bits
     uint32_t inc;
     if (RND == FPEMU_RND_RNE) inc = kHalfM1 + (__umulhi(ac, 1u << (32 - kL)) & 0x00010001u);   // + lsb (ties to even)
     else inc = r2;
-    r = ac + inc;                                                 // a saturated lane has zero low bits: unchanged
+    r = (ac + inc) & kKeep;                                       // a saturated lane has zero low bits: unchanged
   }
-  return (h & kSign2) | (r & kKeep & keep);
+  return as_u32(__hmul2(as_h2(r), keepf));
 }
 
 __device__ __forceinline__ uint32_t bf16x2_nan_lanes(uint32_t r) {
