@@ -88,6 +88,80 @@ __global__ void __launch_bounds__(256) cast_generic_kernel(const CastArgs a, con
   }
 }
 
+// Same rare modes, but aligned buffers: 256-bit vector I/O, one Philox draw per vector, element-wise rounding.
+// (E4M3_IEEE, FP4, RNAZ / RNTZ / RPINF / RNINF, DAZ variants without a packed kernel.)
+// CFMT / CRND >= 0 fix the format / rounding at compile time (the element-wise code then folds to a few dozen
+// instructions); -1 reads them from the arguments.
+template <int DT, int CFMT, int CRND>
+__global__ void __launch_bounds__(kThreads) cast_vec_generic_kernel(const CastArgs a_) {
+  constexpr int VE = DtInfo<DT>::kVecElems;
+  constexpr int U = 2;
+  CastArgs a = a_;
+  if (CFMT >= 0) a.fmt = CFMT;
+  if (CRND >= 0) a.rnd = CRND;
+  const bool scaled = (a.d_scale != nullptr) || (a.scale != 1.0f);
+  float s = 1.0f, rs = 1.0f;
+  if (scaled) {
+    s = effective_scale(a.d_scale ? __ldg(a.d_scale) : a.scale, DT);
+    rs = __frcp_rn(s);
+  }
+  const bool sr = a.rnd == FPEMU_RND_STOCHASTIC;
+  const bool wide = (a.fmt == FPEMU_FMT_BF16 || a.fmt == FPEMU_FMT_FP16);
+  const int64_t nvec = a.n / VE;
+  const char* in = static_cast<const char*>(a.in);
+  char* out = static_cast<char*>(a.out);
+  const int64_t base = (int64_t)blockIdx.x * (kThreads * U) + threadIdx.x;
+  Vec32 v[U];
+#pragma unroll
+  for (int j = 0; j < U; ++j) {
+    const int64_t vi = base + j * kThreads;
+    if (vi < nvec) v[j] = ldg256(in + vi * 32);
+  }
+#pragma unroll
+  for (int j = 0; j < U; ++j) {
+    const int64_t vi = base + j * kThreads;
+    if (vi >= nvec) continue;
+    const uint64_t g0 = a.elem_offset + (uint64_t)vi * VE;
+    // random fields of this vector: 8-bit formats use byte (g % 16) of Philox(g / 16), wide ones 16-bit lane
+    // (g % 8) of Philox(g / 8); a vector never straddles more than two draws
+    uint32_t rw[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
+    if (sr) {
+      const uint4 r0 = philox4x32_10(a.seed_lo, a.seed_hi, wide ? (g0 >> 3) : (g0 >> 4));
+      rw[0] = r0.x; rw[1] = r0.y; rw[2] = r0.z; rw[3] = r0.w;
+      if (wide && VE == 16) {
+        const uint4 r1 = philox4x32_10(a.seed_lo, a.seed_hi, (g0 >> 3) + 1);
+        rw[4] = r1.x; rw[5] = r1.y; rw[6] = r1.z; rw[7] = r1.w;
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < VE / 2; ++k) {
+      float2 f = get_pair<DT>(v[j], k);
+      uint32_t rb0 = 0u, rb1 = 0u;
+      if (sr) {
+        if (wide) {
+          rb0 = rw[k] & 0xFFFFu; rb1 = rw[k] >> 16;
+        } else {
+          const int e0 = (int)(g0 & 15u) + 2 * k;              // byte index of element 2k inside the 16-byte draw
+          rb0 = (rw[e0 >> 2] >> ((e0 & 3) * 8)) & 0xFFu;
+          rb1 = (rw[(e0 + 1) >> 2] >> (((e0 + 1) & 3) * 8)) & 0xFFu;
+        }
+      }
+      f.x = cast_one(f.x, a.fmt, a.rnd, a.flags, scaled, s, rs, DT == FPEMU_DT_F16, rb0);
+      f.y = cast_one(f.y, a.fmt, a.rnd, a.flags, scaled, s, rs, DT == FPEMU_DT_F16, rb1);
+      put_pair<DT>(v[j], k, f);
+    }
+    stg256(out + vi * 32, v[j]);
+  }
+  // ragged tail: element-wise
+  const int64_t e0 = nvec * VE;
+  if (blockIdx.x == gridDim.x - 1 && threadIdx.x < (int)(a.n - e0)) {
+    const int64_t i = e0 + threadIdx.x;
+    const float x = load_elem(a.in, i, DT);
+    const uint32_t rb = sr ? rand_bits_one(a.seed_lo, a.seed_hi, a.elem_offset + (uint64_t)i, wide) : 0u;
+    store_elem(a.out, i, DT, cast_one(x, a.fmt, a.rnd, a.flags, scaled, s, rs, DT == FPEMU_DT_F16, rb));
+  }
+}
+
 // ------------------------------------------------------------------------------------------ dispatch
 typedef void (*CastKernel)(const CastArgs);
 
@@ -119,6 +193,33 @@ static CastKernel pick_rnd(int rnd, bool daz, int dt, bool scaled) {
     case FPEMU_RND_STOCHASTIC: return pick_dt<FMT, FPEMU_RND_STOCHASTIC, false>(dt, scaled);
     default:                   return nullptr;
   }
+}
+
+template <int CFMT, int CRND>
+static CastKernel pick_generic_dt(int dt) {
+  switch (dt) {
+    case FPEMU_DT_F32:  return cast_vec_generic_kernel<FPEMU_DT_F32, CFMT, CRND>;
+    case FPEMU_DT_F16:  return cast_vec_generic_kernel<FPEMU_DT_F16, CFMT, CRND>;
+    default:            return cast_vec_generic_kernel<FPEMU_DT_BF16, CFMT, CRND>;
+  }
+}
+
+// Compile-time specialisations for the rare modes of the reference's grammar; anything else runs the
+// fully run-time variant.
+static CastKernel pick_generic(int fmt, int rnd, int dt) {
+  if (fmt == FPEMU_FMT_E4M3_IEEE) {
+    if (rnd == FPEMU_RND_RNE) return pick_generic_dt<FPEMU_FMT_E4M3_IEEE, FPEMU_RND_RNE>(dt);
+    if (rnd == FPEMU_RND_STOCHASTIC) return pick_generic_dt<FPEMU_FMT_E4M3_IEEE, FPEMU_RND_STOCHASTIC>(dt);
+    if (rnd == FPEMU_RND_RTZ) return pick_generic_dt<FPEMU_FMT_E4M3_IEEE, FPEMU_RND_RTZ>(dt);
+  }
+  if (fmt == FPEMU_FMT_FP4) return pick_generic_dt<FPEMU_FMT_FP4, FPEMU_RND_RNE>(dt);
+  if (fmt == FPEMU_FMT_E5M2) {
+    if (rnd == FPEMU_RND_RNAZ) return pick_generic_dt<FPEMU_FMT_E5M2, FPEMU_RND_RNAZ>(dt);
+    if (rnd == FPEMU_RND_RNTZ) return pick_generic_dt<FPEMU_FMT_E5M2, FPEMU_RND_RNTZ>(dt);
+    if (rnd == FPEMU_RND_RPINF) return pick_generic_dt<FPEMU_FMT_E5M2, FPEMU_RND_RPINF>(dt);
+    if (rnd == FPEMU_RND_RNINF) return pick_generic_dt<FPEMU_FMT_E5M2, FPEMU_RND_RNINF>(dt);
+  }
+  return pick_generic_dt<-1, -1>(dt);
 }
 
 static CastKernel pick_kernel(int fmt, int rnd, bool daz, int dt, bool scaled) {
@@ -161,6 +262,13 @@ int launch_cast(const CastArgs& a, int dtype, cudaStream_t stream) {
     if (want < 1) want = 1;                                  // a launch with only the ragged tail
     if (want > 0x7FFFFFFFLL) return FPEMU_ERR_TOO_LARGE;     // > 2^43 fp32 elements
     k<<<(unsigned)want, kThreads, 0, stream>>>(a);
+  } else if (aligned && rng_ok) {
+    const int ve = dtype == FPEMU_DT_F32 ? 8 : 16;
+    int64_t want = (a.n / ve + kThreads * 2 - 1) / (kThreads * 2);
+    if (want < 1) want = 1;
+    if (want > 0x7FFFFFFFLL) return FPEMU_ERR_TOO_LARGE;
+    CastKernel g = pick_generic(a.fmt, a.rnd, dtype);
+    g<<<(unsigned)want, kThreads, 0, stream>>>(a);
   } else {
     int64_t want = (a.n + 255) / 256;
     const int64_t cap = (int64_t)sms * 8;

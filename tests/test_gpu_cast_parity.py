@@ -22,7 +22,7 @@ DET_MODES = ["E5M2_RTZ", "E5M2_RNE", "E5M2_RNAZ", "E5M2_RNTZ", "E5M2_RPINF", "E5
 GOLDEN_MODES = ["E5M2_RTZ", "E5M2_RNE", "E5M2_RNAZ", "E5M2_RNTZ", "E5M2_RPINF", "E5M2_RNINF",
                 "E5M2_DAZ_RNE", "E5M2_DAZ_RNAZ", "E5M2_DAZ_RNTZ", "E4M3_RNE", "E3M4_RNE",
                 "FLOAT16_RNE", "FLOAT16_DAZ_RNE"]
-SR_MODES = ["E5M2_STOCHASTIC", "E5M2_DAZ_STOCHASTIC", "E4M3_STOCHASTIC", "E3M4_STOCHASTIC",
+SR_MODES = ["E5M2_STOCHASTIC", "E5M2_DAZ_STOCHASTIC", "E4M3_STOCHASTIC", "E3M4_STOCHASTIC", "E4M3_IEEE_STOCHASTIC",
             "BFLOAT16_STOCHASTIC", "FLOAT16_STOCHASTIC"]
 SCALES = [1.0, 0.125, 3.7, 94.09]
 
