@@ -33,6 +33,24 @@ def pytest_collection_modifyitems(config, items):
             item.add_marker(skip)
 
 
+def pytest_sessionstart(session):
+    """Build the native pieces when they are missing (fresh checkout): libfpemu_b200.so needs nvcc (cross-compiles
+    without a GPU), the C oracle needs gcc.  Nothing is rebuilt when the files are already there."""
+    import shutil
+    lib = os.path.join(PKG, "libfpemu_b200.so")
+    if not os.path.exists(lib) and (shutil.which("nvcc") or os.path.exists("/usr/local/cuda/bin/nvcc")):
+        import importlib.util
+        spec = importlib.util.spec_from_file_location("fpemu_b200_build", os.path.join(PKG, "build.py"))
+        b = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(b)
+        b.build()
+    try:
+        from oracle import fpemu_oracle
+        fpemu_oracle.build()
+    except Exception:   # pragma: no cover  (reported by the tests that need it)
+        pass
+
+
 @pytest.fixture(scope="session")
 def golden_dir():
     return os.path.join(ROOT, "tests", "golden")
