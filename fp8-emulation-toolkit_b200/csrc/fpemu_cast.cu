@@ -19,6 +19,11 @@ __global__ void __launch_bounds__(kThreads) cast_vec_kernel(const CastArgs a) {
   sc.unscale32 = (a.flags & FPEMU_FLAG_UNSCALE_FP32) != 0;
   if (SCALED) {
     float s = a.d_scale ? __ldg(a.d_scale) : a.scale;
+    if (a.d_amax != nullptr) {                // per-tensor amax-scaled cast without a separate scale launch
+      s = __fdiv_rn(a.flt_max, __ldg(a.d_amax));
+      if (s > 3.275e4f) s = 6.55e4f;
+      if (a.d_scale_out != nullptr && blockIdx.x == 0 && threadIdx.x == 0) *a.d_scale_out = s;
+    }
     s = effective_scale(s, DT);
     sc.scale = s;
     sc.rscale = __frcp_rn(s);                 // == (float)(1.0 / (double)s): `float r = 1.0 / scale;`
@@ -72,10 +77,16 @@ __global__ void __launch_bounds__(kThreads) cast_vec_kernel(const CastArgs a) {
 
 // Every format x rounding mode, any alignment, per-element random draws.  Correctness path, not the fast one.
 __global__ void __launch_bounds__(256) cast_generic_kernel(const CastArgs a, const int dt) {
-  const bool scaled = (a.d_scale != nullptr) || (a.scale != 1.0f);
+  const bool scaled = (a.d_scale != nullptr) || (a.d_amax != nullptr) || (a.scale != 1.0f);
   float s = 1.0f, rs = 1.0f;
   if (scaled) {
-    s = effective_scale(a.d_scale ? __ldg(a.d_scale) : a.scale, dt);
+    s = a.d_scale ? __ldg(a.d_scale) : a.scale;
+    if (a.d_amax != nullptr) {
+      s = __fdiv_rn(a.flt_max, __ldg(a.d_amax));
+      if (s > 3.275e4f) s = 6.55e4f;
+      if (a.d_scale_out != nullptr && blockIdx.x == 0 && threadIdx.x == 0) *a.d_scale_out = s;
+    }
+    s = effective_scale(s, dt);
     rs = __frcp_rn(s);
   }
   const bool wide = (a.fmt == FPEMU_FMT_BF16 || a.fmt == FPEMU_FMT_FP16);
@@ -99,10 +110,16 @@ __global__ void __launch_bounds__(kThreads) cast_vec_generic_kernel(const CastAr
   CastArgs a = a_;
   if (CFMT >= 0) a.fmt = CFMT;
   if (CRND >= 0) a.rnd = CRND;
-  const bool scaled = (a.d_scale != nullptr) || (a.scale != 1.0f);
+  const bool scaled = (a.d_scale != nullptr) || (a.d_amax != nullptr) || (a.scale != 1.0f);
   float s = 1.0f, rs = 1.0f;
   if (scaled) {
-    s = effective_scale(a.d_scale ? __ldg(a.d_scale) : a.scale, DT);
+    s = a.d_scale ? __ldg(a.d_scale) : a.scale;
+    if (a.d_amax != nullptr) {
+      s = __fdiv_rn(a.flt_max, __ldg(a.d_amax));
+      if (s > 3.275e4f) s = 6.55e4f;
+      if (a.d_scale_out != nullptr && blockIdx.x == 0 && threadIdx.x == 0) *a.d_scale_out = s;
+    }
+    s = effective_scale(s, DT);
     rs = __frcp_rn(s);
   }
   const bool sr = a.rnd == FPEMU_RND_STOCHASTIC;
@@ -247,7 +264,7 @@ int validate_cast(int64_t n, int dtype, int format, int rounding, float scale, c
 
 int launch_cast(const CastArgs& a, int dtype, cudaStream_t stream) {
   if (a.n == 0) return FPEMU_OK;
-  const bool scaled = (a.d_scale != nullptr) || (a.scale != 1.0f);
+  const bool scaled = (a.d_scale != nullptr) || (a.d_amax != nullptr) || (a.scale != 1.0f);
   const bool daz = (a.flags & FPEMU_FLAG_DAZ) != 0;
   const bool aligned = (((uintptr_t)a.in | (uintptr_t)a.out) & 31u) == 0;
   const bool rng_ok = (a.rnd != FPEMU_RND_STOCHASTIC) || ((a.elem_offset & 15u) == 0);
@@ -290,6 +307,7 @@ extern "C" int fpemu_cast(const void* in, void* out, int64_t n, int dtype, int f
   a.seed_lo = (uint32_t)seed; a.seed_hi = (uint32_t)(seed >> 32);
   a.elem_offset = elem_offset;
   a.fmt = format; a.rnd = rounding; a.flags = flags;
+  a.d_amax = nullptr; a.flt_max = 0.0f; a.d_scale_out = nullptr;
   if (format == FPEMU_FMT_BF16 || format == FPEMU_FMT_FP16) { a.scale = 1.0f; a.d_scale = nullptr; }  // no scale in these kernels
   return fpemu::launch_cast(a, dtype, static_cast<cudaStream_t>(stream));
 }

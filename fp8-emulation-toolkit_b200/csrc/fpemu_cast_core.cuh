@@ -14,6 +14,11 @@ struct CastArgs {
   uint32_t seed_lo, seed_hi;
   uint64_t elem_offset;
   int fmt, rnd, flags;
+  // optional: derive the scale from a device-resident absolute maximum inside the cast kernel
+  // (scale = clamp(flt_max / *d_amax), mpemu/qutils.py:283-285); the scale used is written to d_scale_out
+  const float* d_amax;
+  float flt_max;
+  float* d_scale_out;
 };
 
 constexpr int kThreads = 256;

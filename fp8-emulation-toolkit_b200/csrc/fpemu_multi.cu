@@ -254,6 +254,7 @@ extern "C" int fpemu_cast_multi(const void* d_table, const void* h_table, int co
   proto.seed_lo = (uint32_t)seed; proto.seed_hi = (uint32_t)(seed >> 32);
   proto.elem_offset = 0;
   proto.fmt = format; proto.rnd = rounding; proto.flags = flags;
+  proto.d_amax = nullptr; proto.flt_max = 0.0f; proto.d_scale_out = nullptr;
   k<<<h->total_cast, kThreads, 0, static_cast<cudaStream_t>(stream_)>>>(d_table, count, proto, d_scales);
   return (int)cudaGetLastError();
 }

@@ -238,6 +238,7 @@ static RowwiseKernel pick_rowwise(int fmt, int rnd, int dt) {
 }
 
 int validate_cast(int64_t n, int dtype, int format, int rounding, float scale, const void* in, const void* out);
+int launch_cast(const CastArgs& a, int dtype, cudaStream_t stream);
 bool launch_group_reg(const CastArgs& a, int dtype, int64_t groups, int64_t vectors_per_group, int rule, float flt_max,
                       float* d_scale_out, cudaStream_t stream, int* status);
 
@@ -249,6 +250,7 @@ static CastArgs make_args(const void* in, void* out, int64_t n, int format, int 
   a.seed_lo = (uint32_t)seed; a.seed_hi = (uint32_t)(seed >> 32);
   a.elem_offset = elem_offset;
   a.fmt = format; a.rnd = rounding; a.flags = flags;
+  a.d_amax = nullptr; a.flt_max = 0.0f; a.d_scale_out = nullptr;
   return a;
 }
 
@@ -352,4 +354,28 @@ extern "C" int fpemu_cast_rowwise(const void* in, void* out, int64_t rows, int64
   if (k != nullptr) k<<<grid, kThreads, 0, stream>>>(a, rows, cols, flt_max, d_row_scale, clamp);
   else rowwise_generic_kernel<<<grid, 256, 0, stream>>>(a, rows, cols, dtype, flt_max, d_row_scale, clamp);
   return (int)cudaGetLastError();
+}
+
+// Per-tensor amax-scaled cast in ONE call: clears the caller's two-float scratch (d_work[0] = running maximum,
+// d_work[1] = scale used), reduces |x|, and casts with scale = clamp(flt_max / amax) derived inside the cast kernel —
+// three enqueues (memset, amax kernel, cast kernel), no host sync.  Replaces the per-tensor branch of
+// quantize_tensor (mpemu/qutils.py:274-287).
+extern "C" int fpemu_cast_amax_scaled(const void* in, void* out, int64_t n, int dtype, int format, int rounding,
+                                      int flags, float flt_max, float* d_work, uint64_t seed, uint64_t elem_offset,
+                                      void* stream_) {
+  int st = validate_cast(n, dtype, format, rounding, 1.0f, in, out);
+  if (st != FPEMU_OK) return st;
+  if (d_work == nullptr) return FPEMU_ERR_ARG;
+  if (format == FPEMU_FMT_BF16 || format == FPEMU_FMT_FP16) return FPEMU_ERR_MODE;   // these formats take no scale
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  cudaError_t err = cudaMemsetAsync(d_work, 0, 2 * sizeof(float), stream);
+  if (err != cudaSuccess) return (int)err;
+  if (n == 0) return FPEMU_OK;
+  st = fpemu_amax(in, n, dtype, d_work, stream_);
+  if (st != FPEMU_OK) return st;
+  CastArgs a = make_args(in, out, n, format, rounding, flags, seed, elem_offset);
+  a.d_amax = d_work;
+  a.flt_max = flt_max;
+  a.d_scale_out = d_work + 1;
+  return launch_cast(a, dtype, stream);
 }

@@ -137,19 +137,51 @@ def scale_from_amax(d_amax, flt_max, out=None):
     return out
 
 
+_work_cache = {}
+
+
+def _work_for(x, stream):
+    """Two device floats (running maximum, scale) per (device, stream): calls on one stream execute in order, so they
+    can share the scratch; a caller that wants to keep the scale gets a fresh pair instead."""
+    key = (x.device.index, stream)
+    w = _work_cache.get(key)
+    if w is None:
+        w = torch.zeros(2, dtype=torch.float32, device=x.device)
+        _work_cache[key] = w
+    return w
+
+
 def cast_amax_scaled(x, mode, out=None, flt_max=None, seed=None, elem_offset=0, unscale_fp32=False,
                      d_amax=None, return_scale=False):
-    """Per-tensor amax-scaled cast without a host sync: amax kernel -> scale kernel -> cast kernel, all on the
-    current stream (the `per-tensor` / `max` branch of quantize_tensor, qutils.py:274-287).
-    `d_amax` lets a caller supply an already reduced (e.g. all-reduced across ranks) amax."""
-    fmt, _, _ = L.parse_mode(mode)
+    """Per-tensor amax-scaled cast without a host sync (the `per-tensor` / `max` branch of quantize_tensor,
+    qutils.py:274-287).  One library call: memset + amax kernel + cast kernel on the current stream.
+    `d_amax` lets a caller supply an already reduced (e.g. all-reduced across ranks) amax; then only the scale
+    and cast kernels run."""
+    fmt, rnd, flags = L.parse_mode(mode)
     if flt_max is None:
         flt_max = FLT_MAX[fmt]
-    if d_amax is None:
-        d_amax = amax(x)
-    d_scale = scale_from_amax(d_amax, flt_max)
-    y = cast(x, mode, out=out, d_scale=d_scale, seed=seed, elem_offset=elem_offset, unscale_fp32=unscale_fp32)
-    return (y, d_scale) if return_scale else y
+    if d_amax is not None:
+        d_scale = scale_from_amax(d_amax, flt_max)
+        y = cast(x, mode, out=out, d_scale=d_scale, seed=seed, elem_offset=elem_offset, unscale_fp32=unscale_fp32)
+        return (y, d_scale) if return_scale else y
+    _check_tensor(x)
+    if unscale_fp32:
+        flags |= L.FLAG_UNSCALE_FP32
+    if out is None:
+        out = torch.empty_like(x)
+    else:
+        _check_tensor(out, "out")
+        if out.dtype != x.dtype or out.numel() < x.numel():
+            raise ValueError("fpemu: out must match input dtype and size")
+    if rnd == L.RND_STOCHASTIC and seed is None:
+        seed = next_seed()
+    stream = _stream(x)
+    work = torch.zeros(2, dtype=torch.float32, device=x.device) if return_scale else _work_for(x, stream)
+    with _on_device(x):
+        st = L.lib().fpemu_cast_amax_scaled(x.data_ptr(), out.data_ptr(), x.numel(), _dt(x), fmt, rnd, flags,
+                                            float(flt_max), work.data_ptr(), int(seed or 0), int(elem_offset), stream)
+    L.check(st, "fpemu_cast_amax_scaled(%s)" % mode)
+    return (out, work[1:2]) if return_scale else out
 
 
 def cast_amax_scaled_noalloc(x, mode, out, flt_max=None, seed=None, elem_offset=0, unscale_fp32=False):

@@ -124,6 +124,14 @@ FPEMU_API int fpemu_amax(const void* in, int64_t n, int dtype, float* d_amax, vo
  * `scale = 6.55e4 if scale > 3.275e4` (mpemu/qutils.py:283-285).  Device-side, no host sync. */
 FPEMU_API int fpemu_scale_from_amax(const float* d_amax, int count, float flt_max, float* d_scale, void* stream);
 
+/* Per-tensor amax-scaled cast in one call (the per-tensor `max` branch of quantize_tensor, mpemu/qutils.py:274-287):
+ * clears d_work[0..1], reduces max|x| into d_work[0] and casts with scale = clamp(flt_max / amax), which the cast
+ * kernel derives itself and stores in d_work[1].  d_work: two device floats owned by the caller (scratch; calls that
+ * overlap on the GPU need separate d_work).  Three enqueues on `stream`, no host sync. */
+FPEMU_API int fpemu_cast_amax_scaled(const void* in, void* out, int64_t n, int dtype, int format, int rounding,
+                                     int flags, float flt_max, float* d_work, uint64_t seed, uint64_t elem_offset,
+                                     void* stream);
+
 /* Row-wise (per-channel) amax-scaled cast of a rows x cols row-major matrix: each row gets
  * scale = clamp(flt_max / max|row|).  One launch replaces the Python per-channel loop of
  * mpemu/qutils.py:289-311.  d_row_scale (optional, rows floats) receives the scales used. */

@@ -1,0 +1,106 @@
+#!/usr/bin/env python
+"""BASELINE configs[2] and [3] on one GPU through this repo's `mpemu` drop-in: time per forward / training step with
+and without emulation, number of cast launches, time spent inside the cast kernels.
+
+    python tools/module_bench.py [--resnet-batch 64] [--bert-batch 12 --bert-seq 384]"""
+import argparse
+import json
+import os
+import sys
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for p in (ROOT, os.path.join(ROOT, "fp8-emulation-toolkit_b200")):
+    sys.path.insert(0, p)
+from mpemu import mpt_emu  # noqa: E402
+
+
+def timed(fn, reps=5, warm=2):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        fn()
+    torch.cuda.synchronize()
+    return (time.perf_counter() - t0) / reps * 1e3
+
+
+def kernel_time_ms(fn):
+    """Sum of device time of this library's kernels (names contain 'fpemu') and of all kernels, one call."""
+    from torch.profiler import ProfilerActivity, profile
+    fn()
+    torch.cuda.synchronize()
+    with profile(activities=[ProfilerActivity.CUDA]) as prof:
+        fn()
+        torch.cuda.synchronize()
+    ours = total = 0.0
+    n_ours = 0
+    for e in prof.events():
+        if e.device_type == torch.autograd.DeviceType.CUDA:
+            total += e.device_time
+            if "fpemu" in e.name:
+                ours += e.device_time
+                n_ours += 1
+    return ours / 1e3, total / 1e3, n_ours
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--resnet-batch", type=int, default=64)
+    ap.add_argument("--bert-batch", type=int, default=12)
+    ap.add_argument("--bert-seq", type=int, default=384)
+    args = ap.parse_args()
+    out = {}
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = False
+
+    import torchvision
+    torch.manual_seed(0)
+    rn = torchvision.models.resnet50(weights=None).eval().cuda()
+    x = torch.randn(args.resnet_batch, 3, 224, 224, device="cuda")
+    with torch.no_grad():
+        base = timed(lambda: rn(x))
+        t0 = time.perf_counter()
+        rn, emu = mpt_emu.quantize_model(rn, dtype="e4m3", list_exempt_layers=["conv1", "bn1", "fc"], device="cuda")
+        torch.cuda.synchronize()
+        prep = (time.perf_counter() - t0) * 1e3
+        emul = timed(lambda: rn(x))
+        ours, total, n = kernel_time_ms(lambda: rn(x))
+    out["resnet50_ptq_e4m3"] = {"batch": args.resnet_batch, "fp32_forward_ms": base, "emulated_forward_ms": emul,
+                                "quantize_model_ms (53 per-channel weight casts + hooks)": prep,
+                                "cast_kernel_ms_per_forward": ours, "all_kernel_ms_per_forward": total, "cast_launches_per_forward": n}
+
+    from transformers import BertConfig, BertForQuestionAnswering
+    torch.manual_seed(0)
+    cfg = BertConfig()
+    bert = BertForQuestionAnswering(cfg).train().cuda()
+    opt = torch.optim.SGD(bert.parameters(), lr=1e-3)
+    ids = torch.randint(0, cfg.vocab_size, (args.bert_batch, args.bert_seq), device="cuda")
+    sp = torch.randint(0, args.bert_seq, (args.bert_batch,), device="cuda")
+    ep = torch.randint(0, args.bert_seq, (args.bert_batch,), device="cuda")
+
+    def step():
+        opt.zero_grad(set_to_none=True)
+        loss = bert(input_ids=ids, start_positions=sp, end_positions=ep).loss
+        loss.backward()
+        opt.step()
+    base = timed(step)
+    bert, emu = mpt_emu.initialize(bert, None, training_algo="hybrid", list_exempt_layers=["qa_outputs"], device="cuda")
+
+    def estep():
+        opt.zero_grad(set_to_none=True)
+        loss = bert(input_ids=ids, start_positions=sp, end_positions=ep).loss
+        loss.backward()
+        emu.optimizer_step(opt)
+    emul = timed(estep)
+    ours, total, n = kernel_time_ms(estep)
+    out["bert_base_hybrid_step"] = {"batch": args.bert_batch, "seq": args.bert_seq, "fp32_step_ms": base, "emulated_step_ms": emul,
+                                    "cast_kernel_ms_per_step": ours, "all_kernel_ms_per_step": total, "cast_launches_per_step": n}
+    print(json.dumps(out, indent=1))
+
+
+if __name__ == "__main__":
+    main()

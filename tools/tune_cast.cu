@@ -77,7 +77,7 @@ static float time_ms(int reps, const std::function<void()>& f) {
 template <int FMT, int RND, int DT, bool SCALED, int THREADS, int UNROLL>
 void run_cast(const char* name, const void* in, void* out, int64_t n, const std::vector<int>& cps) {
   CastArgs a; a.in = in; a.out = out; a.n = n; a.scale = SCALED ? 3.7f : 1.f; a.d_scale = nullptr; a.seed_lo = 1; a.seed_hi = 2;
-  a.elem_offset = 0; a.fmt = FMT; a.rnd = RND; a.flags = 0;
+  a.elem_offset = 0; a.fmt = FMT; a.rnd = RND; a.flags = 0; a.d_amax = nullptr; a.flt_max = 0.f; a.d_scale_out = nullptr;
   const int ve = DtInfo<DT>::kVecElems; const double bytes = 2.0 * n * DtInfo<DT>::kBytes;
   for (int c : cps) {
     int64_t want = (n / ve + THREADS * UNROLL - 1) / (THREADS * UNROLL);
