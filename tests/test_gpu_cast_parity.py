@@ -455,3 +455,62 @@ def test_no_writes_outside_the_output_buffer(F, dt):
         assert bool((arena[:guard] == sent).all()) and bool((arena[pos:] == sent).all())
         for x, o in zip(xs, outs):
             assert_same(host(o), host(F.cast(x, "E4M3_RNE")), "arena piece")
+
+
+# ------------------------------------------------------------------------------------------ streams and graphs
+def test_runs_on_the_current_torch_stream_without_device_sync(F):
+    """The reference launches on the legacy default stream and synchronises the device (fpemu_kernels.cu:1060-1071);
+    this library must enqueue on torch's CURRENT stream.  A non-blocking side stream first sleeps, then produces the
+    input: a cast issued on any other stream would read the stale zeros."""
+    s = torch.cuda.Stream()
+    x = torch.zeros(1 << 20, device="cuda")
+    with torch.cuda.stream(s):                             # first use loads the kernels (lazy module loading may sync)
+        F.cast(x, "E4M3_RNE")
+        F.cast_amax_scaled(x, "E5M2_RNE")
+    torch.cuda.synchronize()
+    with torch.cuda.stream(s):
+        torch.cuda._sleep(400_000_000)                     # ~0.2 s of GPU time on the side stream
+        x.fill_(1.3)
+        y = F.cast(x, "E4M3_RNE")
+        z = F.cast_amax_scaled(x, "E5M2_RNE")
+    assert not s.query()                                   # the call returned while the stream is still busy: no sync
+    s.synchronize()
+    want = O.cast(np.full(4, 1.3, dtype=np.float32), "E4M3_RNE")[0]
+    assert bool((y == float(want)).all())
+    assert bool((z == 1.3125).all()) or bool((z == z[0]).all() and z[0] != 0)
+
+
+def test_cuda_graph_capture_and_replay(F):
+    """Plain, amax-scaled, row-wise and multi-tensor casts are capture-safe (no allocation, no sync inside the
+    library): capture once, change the input, replay, compare with eager results."""
+    x = torch.randn(1 << 18, device="cuda")
+    y1, y2 = torch.empty_like(x), torch.empty_like(x)
+    m = torch.randn(64, 1024, device="cuda")
+    ym = torch.empty_like(m)
+    parts = [torch.randn(4096, device="cuda") for _ in range(5)]
+    plan = F.MultiTensorPlan(parts, [torch.empty_like(p) for p in parts])
+    side = torch.cuda.Stream()
+    with torch.cuda.stream(side):
+        F.cast(x, "E4M3_STOCHASTIC", out=y1, seed=11)       # warm-up (scratch for the stream gets created here)
+        F.cast_amax_scaled(x, "E4M3_RNE", out=y2)
+        F.cast_rowwise(m, "E3M4_RNE", out=ym)
+        plan.cast("E5M2_RNE")
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=side):
+            F.cast(x, "E4M3_STOCHASTIC", out=y1, seed=11)
+            F.cast_amax_scaled(x, "E4M3_RNE", out=y2)
+            F.cast_rowwise(m, "E3M4_RNE", out=ym)
+            plan.cast("E5M2_RNE")
+    torch.cuda.synchronize()
+    x.mul_(3.0).add_(0.25)
+    m.mul_(0.5)
+    for p in parts:
+        p.add_(1.0)
+    g.replay()
+    torch.cuda.synchronize()
+    assert_same(host(y1), host(F.cast(x, "E4M3_STOCHASTIC", seed=11)), "graph plain")
+    assert_same(host(y2), host(F.cast_amax_scaled(x, "E4M3_RNE")), "graph amax-scaled")
+    assert_same(host(ym), host(F.cast_rowwise(m, "E3M4_RNE")), "graph row-wise")
+    for p, o in zip(parts, plan.outs):
+        assert_same(host(o), host(F.cast(p, "E5M2_RNE")), "graph multi")
