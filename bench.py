@@ -40,6 +40,16 @@ METRIC = "fpemu_cast_throughput"
 UNIT = "GB/s"
 
 
+def workload_config(n):
+    """`config` of the JSON line — identical for both arms (the reference arm times a bounded sample of it)."""
+    return {"workload": "format x rounding QDQ sweep {E5M2,E4M3,E3M4,BFLOAT16}x{RNE,STOCHASTIC,RTZ} + amax-scaled "
+                        "E4M3_RNE on one 2^%d-element fp32 tensor per GPU, out-of-place (BASELINE configs[1])"
+                        % (n.bit_length() - 1),
+            "elems_per_gpu": n, "modes": SWEEP + ["E4M3_RNE_amax_scaled"],
+            "l2": "inputs (%.1f GiB per tensor) larger than L2, no flush" % (4.0 * n / 2 ** 30),
+            "parallelism": "row slabs, one rank per GPU, one 4-byte NCCL all-reduce(MAX) per step"}
+
+
 def measured_peak():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     try:
@@ -169,8 +179,7 @@ def run_reference(args):
     line = {"impl": "reference", "metric": METRIC, "value": gbs, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "format x rounding QDQ sweep, fp32, scale 1 (BASELINE configs[1]); CPU sample size 2^%d elements"
-                                   % (n.bit_length() - 1), "modes": REF_SWEEP},
+            "config": dict(workload_config(args.elems), reference_sample=sample),
             "cpu_baseline": {"value": gbs, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample},
             "e2e": {"value": gbs, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -316,12 +325,7 @@ def run_ours(args):
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "format x rounding QDQ sweep {E5M2,E4M3,E3M4,BFLOAT16}x{RNE,STOCHASTIC,RTZ} + amax-scaled "
-                                   "E4M3_RNE on one 2^%d-element fp32 tensor per GPU, out-of-place (BASELINE configs[1])"
-                                   % (n.bit_length() - 1),
-                       "elems_per_gpu": n, "modes": SWEEP + ["E4M3_RNE_amax_scaled"],
-                       "l2": "inputs (%.1f GiB per tensor) larger than L2, no flush" % (4.0 * n / 2 ** 30),
-                       "parallelism": "row slabs, one rank per GPU, one 4-byte NCCL all-reduce(MAX) per step"},
+            "config": workload_config(n),
             "roofline": {"bound": "hbm", "kernel": "cast_vec_kernel<%s>" % dominant, "achieved": achieved, "peak": peak,
                          "unit": "GB/s", "frac": achieved / peak, "traffic": committed_traffic(dominant),
                          "peak_source": peak_src, "algorithmic_bytes_per_launch": 8 * n,

@@ -45,7 +45,11 @@ __global__ void __launch_bounds__(THREADS) k_copy(const char* in, char* out, int
       int64_t vi = base + j * THREADS;
       if (vi < nvec) {
         if (KIND == 0) v[j] = ldg256(in + vi * 32);
-        else if (KIND == 1) v[j] = *reinterpret_cast<const Vec32*>(in + vi * 32);
+        else if (KIND == 1 || KIND == 3) v[j] = *reinterpret_cast<const Vec32*>(in + vi * 32);
+        else if (KIND == 4) asm volatile("ld.global.cs.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(v[j].w[0]), "=r"(v[j].w[1]), "=r"(v[j].w[2]), "=r"(v[j].w[3]), "=r"(v[j].w[4]), "=r"(v[j].w[5]), "=r"(v[j].w[6]), "=r"(v[j].w[7]) : "l"(in + vi * 32));
+        else if (KIND == 5) asm volatile("ld.global.L1::no_allocate.L2::evict_first.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(v[j].w[0]), "=r"(v[j].w[1]), "=r"(v[j].w[2]), "=r"(v[j].w[3]), "=r"(v[j].w[4]), "=r"(v[j].w[5]), "=r"(v[j].w[6]), "=r"(v[j].w[7]) : "l"(in + vi * 32));
         else asm volatile("ld.global.nc.L1::no_allocate.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                : "=r"(v[j].w[0]), "=r"(v[j].w[1]), "=r"(v[j].w[2]), "=r"(v[j].w[3]), "=r"(v[j].w[4]), "=r"(v[j].w[5]), "=r"(v[j].w[6]), "=r"(v[j].w[7]) : "l"(in + vi * 32));
       }
@@ -55,6 +59,10 @@ __global__ void __launch_bounds__(THREADS) k_copy(const char* in, char* out, int
       int64_t vi = base + j * THREADS;
       if (vi < nvec) {
         if (KIND == 1) *reinterpret_cast<Vec32*>(out + vi * 32) = v[j];
+        else if (KIND == 3 || KIND == 4) asm volatile("st.global.cs.v8.u32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+               :: "l"(out + vi * 32), "r"(v[j].w[0]), "r"(v[j].w[1]), "r"(v[j].w[2]), "r"(v[j].w[3]), "r"(v[j].w[4]), "r"(v[j].w[5]), "r"(v[j].w[6]), "r"(v[j].w[7]) : "memory");
+        else if (KIND == 5) asm volatile("st.global.L1::no_allocate.L2::evict_first.v8.u32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+               :: "l"(out + vi * 32), "r"(v[j].w[0]), "r"(v[j].w[1]), "r"(v[j].w[2]), "r"(v[j].w[3]), "r"(v[j].w[4]), "r"(v[j].w[5]), "r"(v[j].w[6]), "r"(v[j].w[7]) : "memory");
         else stg256(out + vi * 32, v[j]);
       }
     }
@@ -129,6 +137,20 @@ int main(int argc, char** argv) {
   run_copy<512, 2, 0>("copy ld.na.256", in, out, bytes, cps);
   run_copy<256, 2, 1>("copy plain 256", in, out, bytes, cps);
   run_copy<256, 2, 2>("copy ld.nc.na.256", in, out, bytes, cps);
+  if (argc > 2) {   // cache-policy experiments only
+    std::vector<int> one = {0};
+    for (int rep = 0; rep < 3; ++rep) {
+      run_copy<256, 2, 0>("ld.na / st.na", in, out, bytes, one);
+      run_copy<256, 2, 1>("ld / st (default)", in, out, bytes, one);
+      run_copy<256, 2, 3>("ld / st.cs", in, out, bytes, one);
+      run_copy<256, 2, 4>("ld.cs / st.cs", in, out, bytes, one);
+      run_copy<256, 2, 5>("ld.na.evict_first / st.na.evict_first", in, out, bytes, one);
+      run_copy<512, 2, 0>("ld.na / st.na T512", in, out, bytes, one);
+      run_copy<256, 4, 0>("ld.na / st.na U4", in, out, bytes, one);
+      run_copy<128, 2, 0>("ld.na / st.na T128", in, out, bytes, one);
+    }
+    return 0;
+  }
   CASTS(FPEMU_FMT_E5M2, FPEMU_RND_RTZ, FPEMU_DT_F32, false, "E5M2_RTZ f32")
   CASTS(FPEMU_FMT_E5M2, FPEMU_RND_RNE, FPEMU_DT_F32, false, "E5M2_RNE f32")
   CASTS(FPEMU_FMT_E4M3, FPEMU_RND_RNE, FPEMU_DT_F32, false, "E4M3_RNE f32")
