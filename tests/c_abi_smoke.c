@@ -1,0 +1,78 @@
+/* A plain-C caller of libfpemu_b200.so: what a cgo / JNI / FFI binding would do.  Allocates with the CUDA runtime,
+ * casts a small fp32 buffer (E4M3_RNE, scale 1), reduces its amax, derives the scale on the device, runs the blocked
+ * and the multi-tensor entry points, and checks a few known answers.  Exit code 0 = pass.
+ *   gcc -std=c99 -I include tests/c_abi_smoke.c -o c_abi_smoke -L<pkg> -lfpemu_b200 -L/usr/local/cuda/lib64 -lcudart */
+#include <cuda_runtime_api.h>
+#include <math.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "fpemu_b200.h"
+
+#define CHECK(cond, msg) do { if (!(cond)) { fprintf(stderr, "FAIL: %s (line %d)\n", msg, __LINE__); return 1; } } while (0)
+
+int main(void) {
+  int fmt, rnd, flags;
+  CHECK(fpemu_version() > 0, "version");
+  CHECK(fpemu_parse_mode("E4M3_RNE", &fmt, &rnd, &flags) == FPEMU_OK && fmt == FPEMU_FMT_E4M3 && rnd == FPEMU_RND_RNE, "parse");
+  CHECK(fpemu_parse_mode("NOPE", &fmt, &rnd, &flags) == FPEMU_ERR_MODE, "parse rejects");
+  fpemu_parse_mode("E4M3_RNE", &fmt, &rnd, &flags);
+
+  enum { N = 1024 + 5 };
+  float h_in[N], h_out[N];
+  for (int i = 0; i < N; ++i) h_in[i] = 0.001f * (float)(i - 300);
+  h_in[0] = 57344.0f; h_in[1] = -31.0f; h_in[2] = 0.1f; h_in[3] = 0.0009765625f; h_in[4] = INFINITY; h_in[5] = NAN;
+  float *d_in, *d_out, *d_work;
+  CHECK(cudaMalloc((void**)&d_in, sizeof(h_in)) == cudaSuccess, "cudaMalloc");
+  CHECK(cudaMalloc((void**)&d_out, sizeof(h_out)) == cudaSuccess, "cudaMalloc");
+  CHECK(cudaMalloc((void**)&d_work, 64) == cudaSuccess, "cudaMalloc");
+  cudaStream_t s;
+  CHECK(cudaStreamCreate(&s) == cudaSuccess, "stream");
+  cudaMemcpyAsync(d_in, h_in, sizeof(h_in), cudaMemcpyHostToDevice, s);
+
+  int st = fpemu_cast(d_in, d_out, N, FPEMU_DT_F32, fmt, rnd, flags, 1.0f, NULL, 0, 0, s);
+  CHECK(st == FPEMU_OK, fpemu_strerror(st));
+  cudaMemcpyAsync(h_out, d_out, sizeof(h_out), cudaMemcpyDeviceToHost, s);
+  CHECK(cudaStreamSynchronize(s) == cudaSuccess, "sync");
+  CHECK(h_out[0] == 448.0f && h_out[1] == -32.0f && h_out[2] == 0.1015625f && h_out[3] == 0.0f, "known answers");
+  CHECK(h_out[4] == 448.0f && h_out[5] == 448.0f, "Inf and NaN saturate to 448");
+
+  /* amax -> device-side scale -> scaled cast, no host sync in between */
+  cudaMemsetAsync(d_work, 0, 8, s);
+  CHECK(fpemu_amax(d_in + 6, N - 6, FPEMU_DT_F32, d_work, s) == FPEMU_OK, "amax");
+  CHECK(fpemu_scale_from_amax(d_work, 1, 448.0f, d_work + 1, s) == FPEMU_OK, "scale");
+  CHECK(fpemu_cast(d_in + 6, d_out + 6, N - 6, FPEMU_DT_F32, fmt, rnd, flags, 1.0f, d_work + 1, 0, 0, s) == FPEMU_OK, "scaled cast");
+  float work[2];
+  cudaMemcpyAsync(work, d_work, 8, cudaMemcpyDeviceToHost, s);
+  cudaStreamSynchronize(s);
+  CHECK(fabsf(work[0] - 0.001f * 728.0f) < 1e-6f, "amax value");
+  CHECK(work[1] == 448.0f / work[0], "scale = flt_max / amax");
+
+  /* one-call variant gives the same scale */
+  CHECK(fpemu_cast_amax_scaled(d_in + 6, d_out + 6, N - 6, FPEMU_DT_F32, fmt, rnd, flags, 448.0f, d_work + 2, 0, 0, s) == FPEMU_OK, "one-call");
+  float work2[2];
+  cudaMemcpyAsync(work2, d_work + 2, 8, cudaMemcpyDeviceToHost, s);
+  cudaStreamSynchronize(s);
+  CHECK(work2[0] == work[0] && work2[1] == work[1], "one-call scratch");
+
+  /* blocked, row-wise, multi-tensor: status only (values are covered by the Python parity tests) */
+  CHECK(fpemu_cast_blocked(d_in, d_out, 1024, 32, FPEMU_DT_F32, fmt, rnd, flags, 0, 0, s) == FPEMU_OK, "blocked");
+  CHECK(fpemu_cast_rowwise(d_in, d_out, 8, 128, FPEMU_DT_F32, fmt, rnd, flags, 448.0f, NULL, 0, 0, s) == FPEMU_OK, "rowwise");
+  fpemu_tensor_desc descs[2] = {{d_in, d_out, 512, 0}, {d_in + 512, d_out + 512, 512, 512}};
+  long long tb = fpemu_multi_table_bytes(2);
+  void* h_table = malloc((size_t)tb);
+  void* d_table;
+  CHECK(fpemu_multi_table_build(descs, 2, FPEMU_DT_F32, h_table) == FPEMU_OK, "table build");
+  CHECK(cudaMalloc(&d_table, (size_t)tb) == cudaSuccess, "cudaMalloc table");
+  cudaMemcpyAsync(d_table, h_table, (size_t)tb, cudaMemcpyHostToDevice, s);
+  CHECK(fpemu_cast_multi(d_table, h_table, 2, fmt, rnd, flags, NULL, 0, s) == FPEMU_OK, "multi cast");
+  CHECK(fpemu_cast(d_in, d_out, N, 9, fmt, rnd, flags, 1.0f, NULL, 0, 0, s) == FPEMU_ERR_DTYPE, "bad dtype");
+  CHECK(fpemu_cast(d_in, d_out, N, FPEMU_DT_F32, fmt, rnd, flags, 1e6f, NULL, 0, 0, s) == FPEMU_ERR_SCALE, "bad scale");
+  CHECK(cudaStreamSynchronize(s) == cudaSuccess, "final sync");
+  CHECK(cudaGetLastError() == cudaSuccess, "no sticky CUDA error");
+  free(h_table);
+  cudaFree(d_table); cudaFree(d_in); cudaFree(d_out); cudaFree(d_work);
+  printf("c_abi_smoke ok\n");
+  return 0;
+}
