@@ -215,6 +215,13 @@ def quantize_tensor(tensor, qtconfig, qtparams, inplace=False):
         return quantize_to_integer(tensor, mode.split("_")[0], inplace=inplace)
     if not tensor.is_cuda:
         raise RuntimeError("fpemu: the B200 build has no CPU path; move the tensor to a CUDA device")
+    if tensor.dtype == torch.float64:
+        # the reference kernels convert double to float first (fpemu_kernels.cu:98, :126); so does this
+        q = quantize_tensor(tensor.float(), qtconfig, qtparams, inplace=False).to(torch.float64)
+        if inplace:
+            tensor.copy_(q)
+            return tensor
+        return q
     fmt = _L.parse_mode(mode)[0]
     takes_scale = fmt not in (_L.FMT_BF16, _L.FMT_FP16)
     flt_max = qtconfig.get_flt_max()
