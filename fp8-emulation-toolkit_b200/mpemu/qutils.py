@@ -165,6 +165,19 @@ def fpemu_device_fn(tensor, mode, inplace=True, scale=1.0):
         return quantize_to_integer(tensor, mode.split("_")[0], inplace=inplace)
     if not tensor.is_cuda:
         raise RuntimeError("fpemu: the B200 build has no CPU path; move the tensor to a CUDA device")
+    if not (tensor.requires_grad and torch.is_grad_enabled()) and not tensor.is_sparse and mode != 'NONE' \
+            and tensor.dtype != torch.float64:
+        # nothing to record for autograd (weights' .data, gradients, inference): skip the Function wrapper
+        src = tensor if tensor.is_contiguous() else tensor.contiguous()
+        out = src if (inplace and src is tensor) else torch.empty_like(src)
+        if isinstance(scale, torch.Tensor) and scale.is_cuda and scale.dtype == torch.float32 and scale.numel() == 1:
+            _F.cast(src, mode, out=out, d_scale=scale, unscale_fp32=_UNSCALE_FP32)
+        else:
+            _F.cast(src, mode, out=out, scale=float(scale), unscale_fp32=_UNSCALE_FP32)
+        if inplace and src is not tensor:
+            tensor.copy_(out)
+            return tensor
+        return out
     return fpemu_cuda.FPEmuOp.apply(tensor, mode, inplace, scale)
 
 
@@ -176,6 +189,27 @@ def _mean_scale(mean, flt_min, floor):
     mean = mean if mean > floor else flt_min
     scale = float(np.float32(flt_min) / np.float32(mean)) if mean > 0.0 else 1.0
     return 1.0 if scale < 1.0 else scale
+
+
+def _scaled_cast_nograd(tensor, mode, inplace, kind, flt_max, rows, cols, clamp):
+    src = tensor if tensor.is_contiguous() else tensor.contiguous()
+    out = src if (inplace and src is tensor) else torch.empty_like(src)
+    if kind == "tensor":
+        _F.cast_amax_scaled(src, mode, out=out, flt_max=flt_max, unscale_fp32=_UNSCALE_FP32)
+    else:
+        _F.cast_rowwise(src, mode, out=out, flt_max=flt_max, clamp=clamp, rows=rows, cols=cols,
+                        unscale_fp32=_UNSCALE_FP32)
+    if inplace and src is not tensor:
+        tensor.copy_(out)
+        return tensor
+    return out
+
+
+def _scaled_cast(tensor, *args):
+    """Autograd wrapper only where a graph is being recorded (activations in training)."""
+    if tensor.requires_grad and torch.is_grad_enabled():
+        return _ScaledCast.apply(tensor, *args)
+    return _scaled_cast_nograd(tensor, *args)
 
 
 class _ScaledCast(torch.autograd.Function):
@@ -232,7 +266,7 @@ def quantize_tensor(tensor, qtconfig, qtparams, inplace=False):
             scale = _mean_scale(mean, qtconfig.get_flt_min(), 1e-5)
             return fpemu_device_fn(tensor, mode, inplace=inplace, scale=scale)
         if takes_scale and _supported_dtype(tensor):
-            return _ScaledCast.apply(tensor, mode, inplace, "tensor", flt_max, 0, 0, True)
+            return _scaled_cast(tensor, mode, inplace, "tensor", flt_max, 0, 0, True)
         return fpemu_device_fn(tensor, mode, inplace=inplace)
 
     if qtconfig.per_channel is True:
@@ -248,7 +282,7 @@ def quantize_tensor(tensor, qtconfig, qtparams, inplace=False):
                 out.select(0, c).data.copy_(fpemu_device_fn(sub, mode, inplace=False, scale=scale))
             return out
         if takes_scale and _supported_dtype(tensor):
-            return _ScaledCast.apply(tensor, mode, inplace, "rows", flt_max, channels, cols, True)
+            return _scaled_cast(tensor, mode, inplace, "rows", flt_max, channels, cols, True)
         return fpemu_device_fn(tensor, mode, inplace=inplace)
 
     if qtconfig.fine_grained is True:
@@ -260,7 +294,7 @@ def quantize_tensor(tensor, qtconfig, qtparams, inplace=False):
         if (qtconfig.scaling_method == "max" and takes_scale and _supported_dtype(tensor)
                 and tensor.dim() > 1 and in_ch % chunks == 0):
             rows = k * chunks
-            return _ScaledCast.apply(tensor, mode, inplace, "rows", flt_max, rows, tensor.numel() // rows, False)
+            return _scaled_cast(tensor, mode, inplace, "rows", flt_max, rows, tensor.numel() // rows, False)
         out = tensor if inplace else tensor.clone()
         for kk in range(k):
             crs = out.select(0, kk)
