@@ -205,6 +205,20 @@ def test_blocked_vs_reference_cuda_kernels(F, ref_cuda, mode, bs):
     assert_same(host(got), host(want), "%s bs=%d" % (mode, bs))
 
 
+@pytest.mark.parametrize("mode", ["E5M2_RNE", "E4M3_RNE", "E3M4_RNE"])
+@pytest.mark.parametrize("bs", [32, 256, 1024])
+def test_blocked_half_tensors_vs_reference_cuda_kernels(F, ref_cuda, mode, bs):
+    """fp16 tensors: the E5M2 kernel keeps its block scale in half precision (`scalar_t scale`, fpemu_kernels.cu:405-413),
+    E4M3 / E3M4 keep it in float."""
+    rng = np.random.default_rng(9)
+    x = (rng.standard_normal(1 << 16) * np.repeat(np.exp2(rng.integers(-12, 6, 64)), 1024)).astype(np.float16)
+    xt = dev(x)
+    want = ref_cuda.forward(xt.clone(), mode, xt.numel(), False, 1.0, True, bs)[0]
+    got = F.cast_blocked(xt, mode, bs)
+    assert_same(host(got), host(want), "%s half bs=%d" % (mode, bs))
+    assert_same(host(got), O.cast_blocked(x, mode, bs), "%s half bs=%d vs oracle" % (mode, bs))
+
+
 # ------------------------------------------------------------------------------------------ shapes, alignment, in-place
 @pytest.mark.parametrize("n", [0, 1, 7, 8, 9, 15, 16, 17, 31, 255, 1000003])
 @pytest.mark.parametrize("mode", ["E4M3_RNE", "E5M2_STOCHASTIC", "BFLOAT16_RNE"])
