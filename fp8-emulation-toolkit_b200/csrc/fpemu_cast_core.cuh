@@ -41,6 +41,42 @@ __device__ __forceinline__ void put_pair(Vec32& v, int k, float2 f) {
   else v.w[k] = pack_bf16x2_rn(f.x, f.y);
 }
 
+// BFLOAT16 target from fp32 / fp16 tensors: packed path, element-wise redo only for vectors holding a NaN.
+// 16 random bits per element: element g uses 16-bit lane (g % 8) of Philox(g / 8), i.e. pair k of the vector
+// uses word ((2k) % 8) / 2 of call (2k) / 8.
+template <int RND, int DT>
+__device__ __forceinline__ void process_vec_bf16(Vec32& v, const CastArgs& a, uint64_t g0, const uint4& r0, const uint4& r1) {
+  constexpr int kPairs = DtInfo<DT>::kVecElems / 2;
+  constexpr bool kSR = (RND == FPEMU_RND_STOCHASTIC);
+  const Vec32 orig = v;
+  uint32_t nan_any = 0u;
+  uint32_t packed[kPairs];
+#pragma unroll
+  for (int k = 0; k < kPairs; ++k) {
+    const uint4& rr = (k < 4) ? r0 : r1;
+    const int wsel = k & 3;
+    const uint32_t rbits = kSR ? (wsel == 0 ? rr.x : (wsel == 1 ? rr.y : (wsel == 2 ? rr.z : rr.w))) : 0u;
+    const float2 f = get_pair<DT>(v, k);
+    packed[k] = round_pair_bf16<RND>(f.x, f.y, rbits, nan_any);
+  }
+  if (nan_any == 0u) {
+#pragma unroll
+    for (int k = 0; k < kPairs; ++k) put_pair<DT>(v, k, unpack_bf16x2(packed[k]));
+  } else {
+    // rare: redo the vector element by element with the reference's integer rule (keeps NaN payload high bits)
+#pragma unroll
+    for (int k = 0; k < kPairs; ++k) {
+      const uint4& rr = (k < 4) ? r0 : r1;
+      const int wsel = k & 3;
+      const uint32_t rbits = kSR ? (wsel == 0 ? rr.x : (wsel == 1 ? rr.y : (wsel == 2 ? rr.z : rr.w))) : 0u;
+      float2 f = get_pair<DT>(orig, k);
+      f.x = __uint_as_float(round_one_bf16(__float_as_uint(f.x), RND, rbits & 0xFFFFu));
+      f.y = __uint_as_float(round_one_bf16(__float_as_uint(f.y), RND, rbits >> 16));
+      put_pair<DT>(v, k, f);
+    }
+  }
+}
+
 // One 32-byte vector whose first element has global index g0 (a multiple of the vector length).
 template <int FMT, int RND, bool DAZ, int DT, bool SCALED>
 __device__ __forceinline__ void process_vec(Vec32& v, const ScaleCtx& sc, const CastArgs& a, uint64_t g0) {
@@ -101,41 +137,39 @@ __device__ __forceinline__ void process_vec(Vec32& v, const ScaleCtx& sc, const 
       v.w[k] &= ~tiny;
     }
   } else if (FMT == FPEMU_FMT_BF16) {
-    // BFLOAT16 target from fp32 / fp16 tensors: packed path, element-wise redo only for vectors holding a NaN.
-    // 16 random bits per element: element g uses 16-bit lane (g % 8) of Philox(g / 8), i.e. pair k of the vector
-    // uses word ((2k) % 8) / 2 of call (2k) / 8.
-    const Vec32 orig = v;
-    uint32_t nan_any = 0u;
     uint4 r0 = make_uint4(0u, 0u, 0u, 0u), r1 = r0;
     if (kSR) {
       r0 = philox4x32_10(a.seed_lo, a.seed_hi, g0 >> 3);
       if (kPairs > 4) r1 = philox4x32_10(a.seed_lo, a.seed_hi, (g0 >> 3) + 1);
     }
-    uint32_t packed[kPairs];
-#pragma unroll
-    for (int k = 0; k < kPairs; ++k) {
-      const uint4& rr = (k < 4) ? r0 : r1;
-      const int wsel = k & 3;
-      const uint32_t rbits = kSR ? (wsel == 0 ? rr.x : (wsel == 1 ? rr.y : (wsel == 2 ? rr.z : rr.w))) : 0u;
-      const float2 f = get_pair<DT>(v, k);
-      packed[k] = round_pair_bf16<RND>(f.x, f.y, rbits, nan_any);
-    }
-    if (nan_any == 0u) {
-#pragma unroll
-      for (int k = 0; k < kPairs; ++k) put_pair<DT>(v, k, unpack_bf16x2(packed[k]));
-    } else {
-      // rare: redo the vector element by element with the reference's integer rule (keeps NaN payload high bits)
+    if (kSR && DT == FPEMU_DT_F16) {
+      // fp16 tensor, stochastic BFLOAT16: for fp16-normal values only the 3 lowest fp16 mantissa bits are dropped and
+      // only the top 3 of the 16 random bits can carry into the kept part ((m3 << 13) + r16 >= 2^16  <=>  m3 + (r16 >> 13)
+      // >= 8), so the rounding is `(h + (r16 >> 13)) & ~7` on the fp16 encoding itself; a carry into the exponent
+      // reaches Inf exactly where the fp32-domain result (65536) converts back to fp16 Inf.  Zeros become +0.
+      // Vectors with a NaN or a non-zero fp16 subnormal (normalised in fp32: different cut position) take the
+      // general path below.
+      uint32_t special = 0u, q[kPairs];
 #pragma unroll
       for (int k = 0; k < kPairs; ++k) {
         const uint4& rr = (k < 4) ? r0 : r1;
         const int wsel = k & 3;
-        const uint32_t rbits = kSR ? (wsel == 0 ? rr.x : (wsel == 1 ? rr.y : (wsel == 2 ? rr.z : rr.w))) : 0u;
-        float2 f = get_pair<DT>(orig, k);
-        f.x = __uint_as_float(round_one_bf16(__float_as_uint(f.x), RND, rbits & 0xFFFFu));
-        f.y = __uint_as_float(round_one_bf16(__float_as_uint(f.y), RND, rbits >> 16));
-        put_pair<DT>(v, k, f);
+        const uint32_t rbits = wsel == 0 ? rr.x : (wsel == 1 ? rr.y : (wsel == 2 ? rr.z : rr.w));
+        const uint32_t h = v.w[k];
+        const __half2 av = as_h2(h & kAbs2);
+        const uint32_t nrm = __hge2_mask(av, as_h2(h2c(0x0400)));          // normal or Inf (false for NaN)
+        const uint32_t zer = __heq2_mask(av, as_h2(0u));
+        special |= ~(nrm | zer);
+        const uint32_t r3 = __umulhi(rbits, 1u << 19) & 0x00070007u;       // (r16 >> 13) per lane
+        q[k] = (h + r3) & 0xFFF8FFF8u & ~zer;
+      }
+      if (special == 0u) {
+#pragma unroll
+        for (int k = 0; k < kPairs; ++k) v.w[k] = q[k];
+        return;
       }
     }
+    process_vec_bf16<RND, DT>(v, a, g0, r0, r1);
   } else {
     // FLOAT16 target: per element; 13 random bits per element from the same 16-bit lanes as BFLOAT16
     const bool daz = (a.flags & FPEMU_FLAG_DAZ) != 0;
