@@ -195,7 +195,11 @@ def run_ours(args):
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
-    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")       # keep stdout to the one JSON line
+    # keep stdout to the ONE JSON line: libraries (NCCL prints its version banner with printf) write to fd 1, so
+    # fd 1 is pointed at stderr for the whole run and the JSON line goes to a private copy of the real stdout
+    sys.stdout.flush()
+    real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
@@ -343,7 +347,8 @@ def run_ours(args):
                           % (label, len(REF_SWEEP), args.ref_elems.bit_length() - 1)}
         else:
             line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": label}
-    print(json.dumps(line))
+    real_stdout.write(json.dumps(line) + "\n")
+    real_stdout.flush()
     if world > 1:
         dist.destroy_process_group()
     return 0
