@@ -107,6 +107,23 @@ def cast_blocked(x, mode, block_size, out=None, seed=None, elem_offset=0, n=None
     n = x.numel() if n is None else int(n)
     if rnd == L.RND_STOCHASTIC and seed is None:
         seed = next_seed()
+    if int(block_size) == n and n > (1 << 16) and fmt in (L.FMT_E5M2, L.FMT_E4M3, L.FMT_E3M4, L.FMT_E4M3_IEEE) \
+            and not (flags & L.FLAG_DAZ):
+        # one block = the whole (large) tensor (the reference CPU op's reading of block_size == size,
+        # cpp/fpemu_impl.cpp:778-779): amax kernel, then the power-of-two block scale derived on the device from
+        # the exponent field of the maximum (fpemu_kernels.cu:409-413, 577-581, 909-911), then the plain cast
+        a = amax(x, n=n)
+        p2 = (a.view(torch.int32) & 0x7F800000).view(torch.float32)
+        d_scale = 2.0 * p2
+        if fmt == L.FMT_E5M2:
+            if x.dtype == torch.float16:                     # `scalar_t scale` is a half in that instantiation
+                d_scale = (d_scale.half() / 16384.0).float()
+            else:
+                d_scale = d_scale / 16384.0
+        elif fmt in (L.FMT_E4M3, L.FMT_E4M3_IEEE):
+            d_scale = d_scale / 8.0
+        return cast(x, mode, out=out, d_scale=d_scale.contiguous(), seed=seed, elem_offset=elem_offset, n=n,
+                    unscale_fp32=unscale_fp32)
     with _on_device(x):
         st = L.lib().fpemu_cast_blocked(x.data_ptr(), out.data_ptr(), n, int(block_size), _dt(x), fmt, rnd, flags,
                                         int(seed or 0), int(elem_offset), _stream(x))

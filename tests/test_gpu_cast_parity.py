@@ -528,3 +528,18 @@ def test_cuda_graph_capture_and_replay(F):
     assert_same(host(ym), host(F.cast_rowwise(m, "E3M4_RNE")), "graph row-wise")
     for p, o in zip(parts, plan.outs):
         assert_same(host(o), host(F.cast(p, "E5M2_RNE")), "graph multi")
+
+
+@pytest.mark.parametrize("mode", ["E5M2_RNE", "E4M3_RNE", "E3M4_RNE"])
+@pytest.mark.parametrize("dt", ["f32", "f16"])
+def test_blocked_with_one_block_spanning_a_large_tensor(F, mode, dt):
+    """block_size == size: one block = the whole tensor (the reference CPU op's reading, cpp/fpemu_impl.cpp:778-779)."""
+    rng = np.random.default_rng(4)
+    x = (rng.standard_normal(200000) * 0.37).astype(np.float32)
+    if dt == "f16":
+        x = x.astype(np.float16)
+    got = host(F.cast_blocked(dev(x), mode, x.size))
+    assert_same(got, O.cast_blocked(x, mode, x.size), "%s %s whole-tensor block" % (mode, dt))
+    import fpemu_cuda
+    y = fpemu_cuda.forward(dev(x), mode, x.size, False, 1.0, True, x.size)[0]
+    assert_same(host(y), got, "through fpemu_cuda.forward")
