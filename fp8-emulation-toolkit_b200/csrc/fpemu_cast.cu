@@ -14,20 +14,7 @@ namespace fpemu {
 template <int FMT, int RND, bool DAZ, int DT, bool SCALED>
 __global__ void __launch_bounds__(kThreads) cast_vec_kernel(const CastArgs a) {
   constexpr int VE = DtInfo<DT>::kVecElems;
-  ScaleCtx sc;
-  sc.scale = 1.0f; sc.rscale = 1.0f;
-  sc.unscale32 = (a.flags & FPEMU_FLAG_UNSCALE_FP32) != 0;
-  if (SCALED) {
-    float s = a.d_scale ? __ldg(a.d_scale) : a.scale;
-    if (a.d_amax != nullptr) {                // per-tensor amax-scaled cast without a separate scale launch
-      s = __fdiv_rn(a.flt_max, __ldg(a.d_amax));
-      if (s > 3.275e4f) s = 6.55e4f;
-      if (a.d_scale_out != nullptr && blockIdx.x == 0 && threadIdx.x == 0) *a.d_scale_out = s;
-    }
-    s = effective_scale(s, DT);
-    sc.scale = s;
-    sc.rscale = __frcp_rn(s);                 // == (float)(1.0 / (double)s): `float r = 1.0 / scale;`
-  }
+  const ScaleCtx sc = make_scale_ctx<DT, SCALED>(a);
   const int64_t nvec = a.n / VE;
   const char* in = static_cast<const char*>(a.in);
   char* out = static_cast<char*>(a.out);

@@ -77,6 +77,76 @@ __device__ __forceinline__ void process_vec_bf16(Vec32& v, const CastArgs& a, ui
   }
 }
 
+// Scale set-up shared by the vector kernels: host scalar, device scalar, or derived from a device-resident
+// absolute maximum (scale = clamp(flt_max / *d_amax), mpemu/qutils.py:283-285).
+template <int DT, bool SCALED>
+__device__ __forceinline__ ScaleCtx make_scale_ctx(const CastArgs& a) {
+  ScaleCtx sc;
+  sc.scale = 1.0f; sc.rscale = 1.0f;
+  sc.unscale32 = (a.flags & FPEMU_FLAG_UNSCALE_FP32) != 0;
+  if (SCALED) {
+    float s = a.d_scale ? __ldg(a.d_scale) : a.scale;
+    if (a.d_amax != nullptr) {                // per-tensor amax-scaled cast without a separate scale launch
+      s = __fdiv_rn(a.flt_max, __ldg(a.d_amax));
+      if (s > 3.275e4f) s = 6.55e4f;
+      if (a.d_scale_out != nullptr && blockIdx.x == 0 && threadIdx.x == 0) *a.d_scale_out = s;
+    }
+    s = effective_scale(s, DT);
+    sc.scale = s;
+    sc.rscale = __frcp_rn(s);                 // == (float)(1.0 / (double)s): `float r = 1.0 / scale;`
+  }
+  return sc;
+}
+
+// Random bytes of one vector for the 8-bit formats: element g uses byte (g % 16) of Philox(g / 16).
+template <int FMT, int RND, int DT>
+__device__ __forceinline__ void vec_rand_bytes(const CastArgs& a, uint64_t g0, uint32_t (&rw)[4]) {
+  rw[0] = rw[1] = rw[2] = rw[3] = 0u;
+  if (RND == FPEMU_RND_STOCHASTIC) {
+    const uint4 r = philox4x32_10(a.seed_lo, a.seed_hi, g0 >> 4);
+    const uint32_t m = (FMT == FPEMU_FMT_E5M2) ? 0xFFFFFFFFu : (FMT == FPEMU_FMT_E4M3 ? 0x7F7F7F7Fu : 0x3F3F3F3Fu);
+    if (DT == FPEMU_DT_F32) {                       // 8 elements: half of the 16-byte draw
+      const bool hi = (g0 >> 3) & 1u;
+      rw[0] = (hi ? r.z : r.x) & m; rw[1] = (hi ? r.w : r.y) & m;
+    } else {
+      rw[0] = r.x & m; rw[1] = r.y & m; rw[2] = r.z & m; rw[3] = r.w & m;
+    }
+  }
+}
+
+// Pair k of the vector as the fp16x2 encoding the 8-bit roundings start from (scale applied, fp16 RNE).
+template <int DT, bool SCALED>
+__device__ __forceinline__ uint32_t pair_to_h(const Vec32& v, int k, const ScaleCtx& sc) {
+  if (DT == FPEMU_DT_F16 && !SCALED) {
+    // the reference multiplies by scale even when it is 1 (`in[gid] * scale`, fpemu_kernels.cu:420, 588),
+    // which turns every NaN encoding into the canonical 0x7FFF; HMUL2 by 1.0 does the same and is exact
+    // for everything else
+    return as_u32(__hmul2(as_h2(v.w[k]), as_h2(0x3C003C00u)));
+  }
+  float2 f = get_pair<DT>(v, k);
+  if (SCALED) { f.x *= sc.scale; f.y *= sc.scale; }
+  return pack_f16x2_rn(f.x, f.y);
+}
+
+// The rounded fp16x2 pair q -> un-scaled pair k of the output vector.
+template <int DT, bool SCALED>
+__device__ __forceinline__ void finish_pair(Vec32& v, int k, uint32_t q, const ScaleCtx& sc) {
+  if (DT == FPEMU_DT_F16) {
+    if (SCALED) {
+      float2 g = unpack_f16x2(q);
+      q = pack_f16x2_rn(g.x * sc.rscale, g.y * sc.rscale);
+    }
+    v.w[k] = q;
+  } else {
+    float2 g = unpack_f16x2(q);
+    if (SCALED) {
+      g.x *= sc.rscale; g.y *= sc.rscale;
+      if (!sc.unscale32) g = unpack_f16x2(pack_f16x2_rn(g.x, g.y));   // reference CUDA op: through fp16
+    }
+    put_pair<DT>(v, k, g);
+  }
+}
+
 // One 32-byte vector whose first element has global index g0 (a multiple of the vector length).
 template <int FMT, int RND, bool DAZ, int DT, bool SCALED>
 __device__ __forceinline__ void process_vec(Vec32& v, const ScaleCtx& sc, const CastArgs& a, uint64_t g0) {
@@ -84,47 +154,13 @@ __device__ __forceinline__ void process_vec(Vec32& v, const ScaleCtx& sc, const 
   constexpr bool kSR = (RND == FPEMU_RND_STOCHASTIC);
 
   if (FMT == FPEMU_FMT_E5M2 || FMT == FPEMU_FMT_E4M3 || FMT == FPEMU_FMT_E3M4) {
-    // random bytes: element g uses byte (g % 16) of Philox(g / 16)
-    uint32_t rw[4] = {0u, 0u, 0u, 0u};
-    if (kSR) {
-      const uint4 r = philox4x32_10(a.seed_lo, a.seed_hi, g0 >> 4);
-      const uint32_t m = (FMT == FPEMU_FMT_E5M2) ? 0xFFFFFFFFu : (FMT == FPEMU_FMT_E4M3 ? 0x7F7F7F7Fu : 0x3F3F3F3Fu);
-      if (DT == FPEMU_DT_F32) {                       // 8 elements: half of the 16-byte draw
-        const bool hi = (g0 >> 3) & 1u;
-        rw[0] = (hi ? r.z : r.x) & m; rw[1] = (hi ? r.w : r.y) & m;
-      } else {
-        rw[0] = r.x & m; rw[1] = r.y & m; rw[2] = r.z & m; rw[3] = r.w & m;
-      }
-    }
+    uint32_t rw[4];
+    vec_rand_bytes<FMT, RND, DT>(a, g0, rw);
 #pragma unroll
     for (int k = 0; k < kPairs; ++k) {
-      uint32_t h;
-      if (DT == FPEMU_DT_F16 && !SCALED) {
-        // the reference multiplies by scale even when it is 1 (`in[gid] * scale`, fpemu_kernels.cu:420, 588),
-        // which turns every NaN encoding into the canonical 0x7FFF; HMUL2 by 1.0 does the same and is exact
-        // for everything else
-        h = as_u32(__hmul2(as_h2(v.w[k]), as_h2(0x3C003C00u)));
-      } else {
-        float2 f = get_pair<DT>(v, k);
-        if (SCALED) { f.x *= sc.scale; f.y *= sc.scale; }
-        h = pack_f16x2_rn(f.x, f.y);
-      }
+      const uint32_t h = pair_to_h<DT, SCALED>(v, k, sc);
       const uint32_t r2 = kSR ? __byte_perm(rw[k >> 1], 0u, (k & 1) ? 0x4342u : 0x4140u) : 0u;
-      uint32_t q = round_pair<FMT, RND, DAZ>(h, r2);
-      if (DT == FPEMU_DT_F16) {
-        if (SCALED) {
-          float2 g = unpack_f16x2(q);
-          q = pack_f16x2_rn(g.x * sc.rscale, g.y * sc.rscale);
-        }
-        v.w[k] = q;
-      } else {
-        float2 g = unpack_f16x2(q);
-        if (SCALED) {
-          g.x *= sc.rscale; g.y *= sc.rscale;
-          if (!sc.unscale32) g = unpack_f16x2(pack_f16x2_rn(g.x, g.y));   // reference CUDA op: through fp16
-        }
-        put_pair<DT>(v, k, g);
-      }
+      finish_pair<DT, SCALED>(v, k, round_pair<FMT, RND, DAZ>(h, r2), sc);
     }
   } else if (FMT == FPEMU_FMT_BF16 && DT == FPEMU_DT_BF16) {
     // a bf16 tensor cast to BFLOAT16: every rounding mode is the identity (stochastic bits are added below the

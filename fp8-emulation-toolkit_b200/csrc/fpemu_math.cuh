@@ -195,6 +195,61 @@ __device__ __forceinline__ uint32_t round_pair(uint32_t h, uint32_t r2) {
   return round_pair_e4m3_like<FMT, RND>(h, r2);
 }
 
+// ------------------------------------------------------------------------------------------ 8-bit codes
+// Bit layouts are the reference's format table (README.md:17-27): E5M2 = S.EEEEE.MM bias 15 (the top byte of the
+// fp16 encoding), E4M3 = S.EEEE.MMM bias 7, E3M4 = S.EEE.MMMM bias 3, gradual underflow, S.1111.111 / S.111.1111
+// = NaN.  The reference itself never stores these bytes; it only produces the rounded fp16 value q.
+//
+// E4M3 / E3M4: the reference keeps full mantissa precision below the smallest normal (its "pseudo-subnormals",
+// fpemu_kernels.cu:594-606, 924-936), so q can lie between two points of the format's subnormal grid
+// (multiples of 2^-9 / 2^-6).  The code is the nearest grid point, ties to the even code.  In fp16 arithmetic:
+// |q| + M with M = 2.0 / 16.0 has an ulp equal to the subnormal spacing (and is exact for every q at or above
+// the smallest normal), then (t - M) * 2^-(15 - bias) is one exact HFMA2 whose fp16 ENCODING, because fp16's own
+// denormals are gradual too, is the code's magnitude shifted left by 7 / 6.
+// Returns the two codes in the low byte of each 16-bit lane; the high bytes are unspecified.
+template <int FMT>
+__device__ __forceinline__ uint32_t encode_pair(uint32_t q) {
+  if (FMT == FPEMU_FMT_E5M2) return q >> 8;
+  constexpr bool E4 = (FMT == FPEMU_FMT_E4M3);
+  const __half2 t = __hadd2(__habs2(as_h2(q)), as_h2(E4 ? 0x40004000u : 0x4C004C00u));         // |q| + 2.0 / 16.0
+  const uint32_t r = as_u32(__hfma2(t, as_h2(E4 ? 0x1C001C00u : 0x0C000C00u),                   // * 2^-8 / 2^-12
+                                    as_h2(E4 ? 0xA000A000u : 0x9C009C00u)));                     // - 2^-7 / 2^-8
+  const uint32_t mag = __umulhi(r, 1u << (E4 ? 25 : 26));                                        // r >> 7 / 6
+  const uint32_t sgn = __umulhi(q, 1u << 24);                                                    // sign -> bit 7
+  uint32_t code;                                                                                 // bits 0-6 of mag, rest of sgn
+  asm("lop3.b32 %0, %1, %2, 0x007F007F, 0xE4;" : "=r"(code) : "r"(mag), "r"(sgn));
+  return code;
+}
+
+// Two codes (low byte of each 16-bit lane, high bytes zero) -> the fp16x2 value they denote.
+template <int FMT>
+__device__ __forceinline__ uint32_t decode_pair(uint32_t c2) {
+  if (FMT == FPEMU_FMT_E5M2) return c2 << 8;
+  constexpr bool E4 = (FMT == FPEMU_FMT_E4M3);
+  const uint32_t bits = (c2 << (E4 ? 7 : 6)) & (E4 ? 0x3F803F80u : 0x1FC01FC0u);
+  const uint32_t nan = __heq2_mask(as_h2(bits), as_h2(E4 ? 0x3F803F80u : 0x1FC01FC0u));         // S.1111.111
+  const uint32_t mag = as_u32(__hmul2(as_h2(bits), as_h2(E4 ? 0x5C005C00u : 0x6C006C00u)));     // * 2^8 / 2^12, exact
+  return mag | (nan & kAbs2) | ((c2 << 8) & kSign2);
+}
+
+// Element-wise forms of the same two maps (generic kernels, ragged tails).
+__device__ __forceinline__ uint32_t encode_one(uint32_t q, int fmt) {
+  if (fmt == FPEMU_FMT_E5M2) return (q >> 8) & 0xFFu;
+  const bool e4 = (fmt == FPEMU_FMT_E4M3);
+  const __half a = __ushort_as_half((unsigned short)(q & 0x7FFFu));
+  const __half t = __hadd(a, __ushort_as_half(e4 ? 0x4000 : 0x4C00));
+  const __half r = __hfma(t, __ushort_as_half(e4 ? 0x1C00 : 0x0C00), __ushort_as_half(e4 ? 0xA000 : 0x9C00));
+  return (((uint32_t)__half_as_ushort(r) >> (e4 ? 7 : 6)) & 0x7Fu) | ((q >> 8) & 0x80u);
+}
+__device__ __forceinline__ uint32_t decode_one(uint32_t c, int fmt) {
+  if (fmt == FPEMU_FMT_E5M2) return (c & 0xFFu) << 8;
+  const bool e4 = (fmt == FPEMU_FMT_E4M3);
+  const uint32_t m = c & 0x7Fu, sign = (c & 0x80u) << 8;
+  if (m == 0x7Fu) return sign | 0x7FFFu;
+  const __half v = __hmul(__ushort_as_half((unsigned short)(m << (e4 ? 7 : 6))), __ushort_as_half(e4 ? 0x5C00 : 0x6C00));
+  return sign | __half_as_ushort(v);
+}
+
 // ------------------------------------------------------------------------------------------ one element
 // Rounding increment decision shared by every format: `v` is the integer whose low L bits get dropped.
 __device__ __forceinline__ uint32_t round_up_bit(uint32_t v, int L, int rnd, bool pos, bool neg) {

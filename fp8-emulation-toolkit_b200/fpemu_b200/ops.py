@@ -97,6 +97,62 @@ def cast(x, mode, out=None, scale=1.0, d_scale=None, seed=None, elem_offset=0, n
     return out
 
 
+def _d_scale_ptr(d_scale):
+    if d_scale is None:
+        return None
+    if not (d_scale.is_cuda and d_scale.dtype == torch.float32 and d_scale.numel() >= 1):
+        raise ValueError("fpemu: d_scale must be a float32 CUDA tensor")
+    return d_scale.data_ptr()
+
+
+def encode(x, mode, out=None, scale=1.0, d_scale=None, seed=None, elem_offset=0, n=None):
+    """Round `x` like `cast(x, mode, ...)` and return the format's one-byte codes (uint8 tensor of x's shape):
+    E5M2 / E4M3 / E3M4 bit layouts of the reference's format table (README.md:17-27)."""
+    _check_tensor(x)
+    fmt, rnd, flags = L.parse_mode(mode)
+    n = x.numel() if n is None else int(n)
+    if n > x.numel():
+        raise ValueError("fpemu: size larger than the tensor")
+    if out is None:
+        out = torch.empty(x.shape, dtype=torch.uint8, device=x.device)
+    elif not (out.is_cuda and out.dtype == torch.uint8 and out.is_contiguous() and out.numel() >= n):
+        raise ValueError("fpemu: codes must be a contiguous uint8 CUDA tensor of at least n elements")
+    if rnd == L.RND_STOCHASTIC and seed is None:
+        seed = next_seed()
+    with _on_device(x):
+        st = L.lib().fpemu_encode(x.data_ptr(), out.data_ptr(), n, _dt(x), fmt, rnd, flags, float(scale),
+                                  _d_scale_ptr(d_scale), int(seed or 0), int(elem_offset), _stream(x))
+    L.check(st, "fpemu_encode(%s)" % mode)
+    return out
+
+
+def decode(codes, mode, dtype=torch.float32, out=None, scale=1.0, d_scale=None, n=None, unscale_fp32=False):
+    """Codes written by `encode` -> values of `dtype`, divided by the scale exactly as `cast` un-scales.
+    `mode` may be a full mode string or just the format name ("E4M3")."""
+    if not (codes.is_cuda and codes.dtype == torch.uint8 and codes.is_contiguous()):
+        raise ValueError("fpemu: codes must be a contiguous uint8 CUDA tensor")
+    fmt = {"E5M2": L.FMT_E5M2, "E4M3": L.FMT_E4M3, "E3M4": L.FMT_E3M4}.get(mode)
+    if fmt is None:
+        fmt = L.parse_mode(mode)[0]
+    flags = 0
+    if unscale_fp32:
+        flags |= L.FLAG_UNSCALE_FP32
+    n = codes.numel() if n is None else int(n)
+    if n > codes.numel():
+        raise ValueError("fpemu: size larger than the tensor")
+    if out is None:
+        out = torch.empty(codes.shape, dtype=dtype, device=codes.device)
+    else:
+        _check_tensor(out, "out")
+        if out.numel() < n:
+            raise ValueError("fpemu: out too small")
+    with _on_device(codes):
+        st = L.lib().fpemu_decode(codes.data_ptr(), out.data_ptr(), n, _dt(out), fmt, flags, float(scale),
+                                  _d_scale_ptr(d_scale), _stream(codes))
+    L.check(st, "fpemu_decode(%s)" % mode)
+    return out
+
+
 def cast_blocked(x, mode, block_size, out=None, seed=None, elem_offset=0, n=None, unscale_fp32=False):
     _check_tensor(x)
     fmt, rnd, flags = L.parse_mode(mode)

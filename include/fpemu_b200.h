@@ -139,6 +139,27 @@ FPEMU_API int fpemu_cast_rowwise(const void* in, void* out, int64_t rows, int64_
                        int rounding, int flags, float flt_max, float* d_row_scale, uint64_t seed,
                        uint64_t elem_offset, void* stream);
 
+/* ---- 8-bit wire form --------------------------------------------------------------
+ * The reference defines the E5M2 / E4M3 / E3M4 bit layouts (README.md:17-27) but only ever produces the
+ * de-quantised value; these two entry points materialise the byte.
+ *
+ * fpemu_encode: the rounding of fpemu_cast (same arguments, same random fields for stochastic rounding), result
+ * stored as one code per element: E5M2 S.EEEEE.MM bias 15 (Inf 0x7C, NaN 0x7D-0x7F), E4M3 S.EEEE.MMM bias 7
+ * (max 0x7E = 448, 0x7F = NaN, never produced), E3M4 S.EEE.MMMM bias 3 (max 0x7E = 30), gradual underflow.
+ * format must be one of those three.  Where the reference's rounded value lies between two points of the
+ * format's subnormal grid (E4M3 below 2^-6, E3M4 below 2^-2: the reference keeps full mantissa precision there,
+ * fpemu_kernels.cu:594-606, 924-936) the code is the nearest grid point, ties to the even code.
+ * Fast path: `in` 32-byte aligned, `codes` 8-byte (fp32 input) / 16-byte (16-bit input) aligned, elem_offset a
+ * multiple of 16 when rounding is stochastic; otherwise an element-wise kernel runs.
+ *
+ * fpemu_decode: codes -> values of element type `dtype`, multiplied by 1/scale exactly as fpemu_cast un-scales
+ * (FPEMU_FLAG_UNSCALE_FP32 honoured).  fpemu_decode(fpemu_encode(x)) equals fpemu_cast(x) bit for bit for every
+ * element whose rounded value is a member of the format (always, for E5M2). */
+FPEMU_API int fpemu_encode(const void* in, void* codes, int64_t n, int dtype, int format, int rounding, int flags,
+                 float scale, const float* d_scale, uint64_t seed, uint64_t elem_offset, void* stream);
+FPEMU_API int fpemu_decode(const void* codes, void* out, int64_t n, int dtype, int format, int flags, float scale,
+                 const float* d_scale, void* stream);
+
 /* Host-buffer convenience used by the end-to-end measurement: casts n elements that live in HOST
  * memory (pinned for full speed) into a HOST output, staging through two caller-provided device
  * buffers of chunk_elems elements each (d_stage[0], d_stage[1]) so the H2D copy, the kernel and the

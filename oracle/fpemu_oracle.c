@@ -385,8 +385,9 @@ static float recip_f32(float s) { return (float)(1.0 / (double)s); }  /* `float 
  * `scale_h16` says the E5M2 kernels hold it (and multiply) in half precision — the at::Half
  * instantiation declares `scalar_t scale` (cuda/fpemu_kernels.cu:405,420,469,497) while E4M3/E3M4
  * declare `float scale = in_scale` (:573, :903). */
-static float cast_one_h16(float x, int dtype, int format, int rmode, int flags, float scale, float rscale,
-                          uint32_t rnd) {
+static float kernel_scale(float scale, int dtype);
+
+static uint16_t quantize_h16(float x, int dtype, int format, int rmode, int flags, float scale, uint32_t rnd) {
   float inval;
   if (dtype == FPEMU_DT_F16 && format == FPEMU_FMT_E5M2)
     inval = fpemu_oracle_half2float(fpemu_oracle_float2half(x * scale));   /* Half * Half -> Half */
@@ -399,10 +400,88 @@ static float cast_one_h16(float x, int dtype, int format, int rmode, int flags, 
     case FPEMU_FMT_E3M4:      h = round_e3m4(h, rmode, rnd); break;
     default:                  h = round_e4m3_ieee(h, rmode, rnd); break;
   }
+  return h;
+}
+
+static float unscale_h16(uint16_t h, int flags, float rscale) {
   float q = fpemu_oracle_half2float(h) * rscale;
   if (!(flags & FPEMU_FLAG_UNSCALE_FP32))
     q = fpemu_oracle_half2float(fpemu_oracle_float2half(q));
   return q;
+}
+
+static float cast_one_h16(float x, int dtype, int format, int rmode, int flags, float scale, float rscale,
+                          uint32_t rnd) {
+  return unscale_h16(quantize_h16(x, dtype, format, rmode, flags, scale, rnd), flags, rscale);
+}
+
+/* ---- 8-bit codes.  Bit layouts: the reference's format table, README.md:17-27 (E5M2 S.EEEEE.MM bias 15,
+ * E4M3 S.EEEE.MMM bias 7, E3M4 S.EEE.MMMM bias 3; S.1111.111 / S.111.1111 = NaN; gradual underflow).  The
+ * reference never stores the byte, so these two maps have no reference code to follow; they are written with
+ * integer arithmetic only, independently of the CUDA kernels' fp16-FMA formulation.  A rounded value the
+ * reference leaves between two subnormal grid points (its pseudo-subnormals keep full mantissa precision,
+ * cuda/fpemu_kernels.cu:594-606, 924-936) goes to the nearest grid point, ties to the even code. */
+static unsigned rne_shift(unsigned v, int s) {
+  if (s <= 0) return v << (-s);
+  if (s > 31) return 0u;
+  unsigned q = v >> s, rem = v & ((1u << s) - 1u), half = 1u << (s - 1);
+  if (rem > half || (rem == half && (q & 1u))) ++q;
+  return q;
+}
+
+uint8_t fpemu_oracle_code_from_h16(uint16_t q, int format) {
+  if (format == FPEMU_FMT_E5M2) return (uint8_t)(q >> 8);
+  const int mbits = (format == FPEMU_FMT_E4M3) ? 3 : 4;          /* stored mantissa bits          */
+  const int bias = (format == FPEMU_FMT_E4M3) ? 7 : 3;
+  const unsigned a = q & 0x7FFFu, sign = (q >> 8) & 0x80u;
+  const int e5 = (int)(a >> 10);
+  const int min_normal_e5 = 15 + (1 - bias);                      /* fp16 exponent field of 2^(1-bias) */
+  unsigned mag;
+  if (e5 >= min_normal_e5) {
+    mag = (a >> (10 - mbits)) - ((unsigned)(15 - bias) << mbits);
+  } else {
+    /* value = mant * 2^(e - 25); subnormal grid spacing = 2^(1 - bias - mbits) */
+    const unsigned mant = e5 ? (0x400u | (a & 0x3FFu)) : (a & 0x3FFu);
+    const int e = e5 ? e5 : 1;
+    mag = rne_shift(mant, (1 - bias - mbits) - (e - 25));
+  }
+  return (uint8_t)(sign | mag);
+}
+
+uint16_t fpemu_oracle_h16_from_code(uint8_t c, int format) {
+  if (format == FPEMU_FMT_E5M2) return (uint16_t)(c << 8);
+  const int mbits = (format == FPEMU_FMT_E4M3) ? 3 : 4;
+  const int bias = (format == FPEMU_FMT_E4M3) ? 7 : 3;
+  const unsigned m = c & 0x7Fu, sign = (unsigned)(c & 0x80u) << 8;
+  if (m == 0x7Fu) return (uint16_t)(sign | 0x7FFFu);
+  const unsigned E = m >> mbits, M = m & ((1u << mbits) - 1u);
+  if (E == 0) {                                                   /* M * 2^(1 - bias - mbits), exact in fp16 */
+    f32_t v; v.f = (float)M;
+    if (M) v.u += (uint32_t)(1 - bias - mbits) << 23;
+    return (uint16_t)(sign | fpemu_oracle_float2half(v.f));
+  }
+  return (uint16_t)(sign | ((E + 15 - bias) << 10) | (M << (10 - mbits)));
+}
+
+int fpemu_oracle_encode(const void* in, uint8_t* codes, int64_t n, int dtype, int format, int rounding, int flags,
+                        float scale, const uint32_t* rnd) {
+  if (n < 0 || dtype < 0 || dtype >= FPEMU_DT_COUNT) return FPEMU_ERR_ARG;
+  if (format != FPEMU_FMT_E5M2 && format != FPEMU_FMT_E4M3 && format != FPEMU_FMT_E3M4) return FPEMU_ERR_MODE;
+  if (scale > 65504.0f) return FPEMU_ERR_SCALE;
+  const float ks = kernel_scale(scale, dtype);
+  for (int64_t i = 0; i < n; ++i)
+    codes[i] = fpemu_oracle_code_from_h16(
+        quantize_h16(load_elem(in, i, dtype), dtype, format, rounding, flags, ks, rnd ? rnd[i] : 0u), format);
+  return FPEMU_OK;
+}
+
+int fpemu_oracle_decode(const uint8_t* codes, void* out, int64_t n, int dtype, int format, int flags, float scale) {
+  if (n < 0 || dtype < 0 || dtype >= FPEMU_DT_COUNT) return FPEMU_ERR_ARG;
+  if (format != FPEMU_FMT_E5M2 && format != FPEMU_FMT_E4M3 && format != FPEMU_FMT_E3M4) return FPEMU_ERR_MODE;
+  const float rs = recip_f32(kernel_scale(scale, dtype));
+  for (int64_t i = 0; i < n; ++i)
+    store_elem(out, i, dtype, unscale_h16(fpemu_oracle_h16_from_code(codes[i], format), flags, rs));
+  return FPEMU_OK;
 }
 
 /* The scale a kernel instantiated for `dtype` actually sees: `const scalar_t in_scale` rounds the

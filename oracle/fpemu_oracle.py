@@ -59,6 +59,14 @@ def lib():
         L.fpemu_oracle_float2half.restype = ctypes.c_uint16
         L.fpemu_oracle_half2float.argtypes = [ctypes.c_uint16]
         L.fpemu_oracle_half2float.restype = f32
+        L.fpemu_oracle_encode.argtypes = [vp, vp, i64, i32, i32, i32, i32, f32, vp]
+        L.fpemu_oracle_encode.restype = i32
+        L.fpemu_oracle_decode.argtypes = [vp, vp, i64, i32, i32, i32, f32]
+        L.fpemu_oracle_decode.restype = i32
+        L.fpemu_oracle_code_from_h16.argtypes = [ctypes.c_uint16, i32]
+        L.fpemu_oracle_code_from_h16.restype = ctypes.c_uint8
+        L.fpemu_oracle_h16_from_code.argtypes = [ctypes.c_uint8, i32]
+        L.fpemu_oracle_h16_from_code.restype = ctypes.c_uint16
         _lib = L
     return _lib
 
@@ -117,6 +125,35 @@ def cast(x, mode, scale=1.0, unscale_fp32=False, seed=0, elem_offset=0, rand=Non
                                  float(scale), rptr)
     if st != 0:
         raise ValueError("fpemu_oracle_cast status %d" % st)
+    return out
+
+
+def encode(x, mode, scale=1.0, seed=0, elem_offset=0, rand=None):
+    """The rounding of `cast`, returned as the format's one-byte codes (uint8 array)."""
+    x = np.ascontiguousarray(x)
+    fmt, rnd, flags = parse_mode(mode)
+    out = np.empty(x.shape, dtype=np.uint8)
+    rptr = None
+    if rnd == RND["STOCHASTIC"]:
+        if rand is None:
+            rand = rand_bits(seed, elem_offset, x.size, fmt)
+        rand = np.ascontiguousarray(rand, dtype=np.uint32)
+        rptr = rand.ctypes.data
+    st = lib().fpemu_oracle_encode(x.ctypes.data, out.ctypes.data, x.size, _np_dtype_code(x), fmt, rnd, flags,
+                                   float(scale), rptr)
+    if st != 0:
+        raise ValueError("fpemu_oracle_encode status %d" % st)
+    return out
+
+
+def decode(codes, fmt_name, dtype=np.float32, scale=1.0, unscale_fp32=False):
+    """Codes -> values (`dtype`: np.float32, np.float16, or np.uint16 for bf16 bit patterns), un-scaled like `cast`."""
+    codes = np.ascontiguousarray(codes, dtype=np.uint8)
+    out = np.empty(codes.shape, dtype=dtype)
+    st = lib().fpemu_oracle_decode(codes.ctypes.data, out.ctypes.data, codes.size, _np_dtype_code(out), FMT[fmt_name],
+                                   FLAG_UNSCALE_FP32 if unscale_fp32 else 0, float(scale))
+    if st != 0:
+        raise ValueError("fpemu_oracle_decode status %d" % st)
     return out
 
 

@@ -67,6 +67,18 @@ int main(void) {
   CHECK(cudaMalloc(&d_table, (size_t)tb) == cudaSuccess, "cudaMalloc table");
   cudaMemcpyAsync(d_table, h_table, (size_t)tb, cudaMemcpyHostToDevice, s);
   CHECK(fpemu_cast_multi(d_table, h_table, 2, fmt, rnd, flags, NULL, 0, s) == FPEMU_OK, "multi cast");
+  /* 8-bit wire form: known codes from the format table (README.md:17-27), then a round trip */
+  unsigned char* d_codes; unsigned char h_codes[8];
+  CHECK(cudaMalloc((void**)&d_codes, N) == cudaSuccess, "cudaMalloc");
+  CHECK(fpemu_encode(d_in, d_codes, N, FPEMU_DT_F32, fmt, rnd, flags, 1.0f, NULL, 0, 0, s) == FPEMU_OK, "encode");
+  CHECK(fpemu_decode(d_codes, d_out, N, FPEMU_DT_F32, fmt, 0, 1.0f, NULL, s) == FPEMU_OK, "decode");
+  cudaMemcpyAsync(h_codes, d_codes, 8, cudaMemcpyDeviceToHost, s);
+  cudaMemcpyAsync(h_out, d_out, sizeof(h_out), cudaMemcpyDeviceToHost, s);
+  CHECK(cudaStreamSynchronize(s) == cudaSuccess, "sync");
+  CHECK(h_codes[0] == 0x7E && h_codes[1] == 0xE0 && h_codes[3] == 0x00 && h_codes[4] == 0x7E, "known codes");
+  CHECK(h_out[0] == 448.0f && h_out[1] == -32.0f && h_out[2] == 0.1015625f && h_out[3] == 0.0f, "round trip");
+  CHECK(fpemu_encode(d_in, d_codes, N, FPEMU_DT_F32, FPEMU_FMT_BF16, rnd, flags, 1.0f, NULL, 0, 0, s) == FPEMU_ERR_MODE, "encode rejects 16-bit formats");
+  cudaFree(d_codes);
   CHECK(fpemu_cast(d_in, d_out, N, 9, fmt, rnd, flags, 1.0f, NULL, 0, 0, s) == FPEMU_ERR_DTYPE, "bad dtype");
   CHECK(fpemu_cast(d_in, d_out, N, FPEMU_DT_F32, fmt, rnd, flags, 1e6f, NULL, 0, 0, s) == FPEMU_ERR_SCALE, "bad scale");
   CHECK(cudaStreamSynchronize(s) == cudaSuccess, "final sync");
