@@ -7,6 +7,7 @@
 // passes its device address to the launches.  CTA b of a launch finds its tensor by comparing b against the
 // per-tensor first-CTA indices in the table (one coalesced table read per CTA, one ballot), then runs the same
 // per-vector code as the single-tensor kernels.
+#include "fpemu_codec_core.cuh"
 #include "fpemu_reduce.cuh"
 
 namespace fpemu {
@@ -116,6 +117,31 @@ __global__ void __launch_bounds__(kThreads) cast_multi_kernel(const void* table,
   }
 }
 
+// Same CTA numbering as cast_multi_kernel (so one table serves both), codes instead of values: the table's `out`
+// pointers are the byte buffers.
+template <int FMT, int RND, int DT, bool SCALED>
+__global__ void __launch_bounds__(kThreads) encode_multi_kernel(const void* table, const int count, const CastArgs proto,
+                                                               const float* d_scales) {
+  constexpr int VE = DtInfo<DT>::kVecElems;
+  constexpr int U = UnrollFor<DT>::value;
+  const int t = mt_find<false>(table, count, blockIdx.x);
+  const MtEntry e = mt_entries(table)[t];
+  CastArgs a = proto;
+  a.in = e.in; a.out = e.out; a.n = e.n; a.elem_offset = e.elem_offset;
+  a.seed_lo = proto.seed_lo + (uint32_t)t;                       // tensor t uses seed + t
+  a.seed_hi = proto.seed_hi + (a.seed_lo < proto.seed_lo ? 1u : 0u);
+  ScaleCtx sc;
+  sc.scale = 1.0f; sc.rscale = 1.0f; sc.unscale32 = false;
+  if (SCALED) {
+    const float s = effective_scale(__ldg(d_scales + t), DT);
+    sc.scale = s;
+    sc.rscale = __frcp_rn(s);
+  }
+  const int64_t local_cta = (int64_t)(blockIdx.x - e.cta_cast);
+  const int64_t ctas_of_t = (a.n / VE + kThreads * U - 1) / (kThreads * U);
+  encode_cta<FMT, RND, false, DT, SCALED, U>(a, sc, local_cta, local_cta == (ctas_of_t > 0 ? ctas_of_t - 1 : 0));
+}
+
 template <int DT>
 __global__ void __launch_bounds__(kThreads) amax_multi_kernel(const void* table, const int count, float* d_amax) {
   constexpr int VE = DtInfo<DT>::kVecElems;
@@ -173,6 +199,24 @@ static MultiCastKernel mpick_rnd(int rnd, int dt, bool scaled) {
     case FPEMU_RND_RNE:        return mpick_dt<FMT, FPEMU_RND_RNE>(dt, scaled);
     case FPEMU_RND_RTZ:        return (FMT == FPEMU_FMT_FP16) ? nullptr : mpick_dt<FMT, FPEMU_RND_RTZ>(dt, scaled);
     case FPEMU_RND_STOCHASTIC: return mpick_dt<FMT, FPEMU_RND_STOCHASTIC>(dt, scaled);
+    default:                   return nullptr;
+  }
+}
+
+template <int FMT, int RND>
+static MultiCastKernel epick_dt(int dt, bool scaled) {
+  switch (dt) {
+    case FPEMU_DT_F32:  return scaled ? encode_multi_kernel<FMT, RND, FPEMU_DT_F32, true> : encode_multi_kernel<FMT, RND, FPEMU_DT_F32, false>;
+    case FPEMU_DT_F16:  return scaled ? encode_multi_kernel<FMT, RND, FPEMU_DT_F16, true> : encode_multi_kernel<FMT, RND, FPEMU_DT_F16, false>;
+    default:            return scaled ? encode_multi_kernel<FMT, RND, FPEMU_DT_BF16, true> : encode_multi_kernel<FMT, RND, FPEMU_DT_BF16, false>;
+  }
+}
+template <int FMT>
+static MultiCastKernel epick_rnd(int rnd, int dt, bool scaled) {
+  switch (rnd) {
+    case FPEMU_RND_RNE:        return epick_dt<FMT, FPEMU_RND_RNE>(dt, scaled);
+    case FPEMU_RND_RTZ:        return epick_dt<FMT, FPEMU_RND_RTZ>(dt, scaled);
+    case FPEMU_RND_STOCHASTIC: return epick_dt<FMT, FPEMU_RND_STOCHASTIC>(dt, scaled);
     default:                   return nullptr;
   }
 }
@@ -247,6 +291,34 @@ extern "C" int fpemu_cast_multi(const void* d_table, const void* h_table, int co
     default: break;
   }
   if (k == nullptr) return FPEMU_ERR_MODE;                       // rare modes: use the per-tensor entry point
+  if (h->total_cast == 0) return FPEMU_OK;
+  CastArgs proto;
+  proto.in = nullptr; proto.out = nullptr; proto.n = 0;
+  proto.scale = 1.0f; proto.d_scale = nullptr;
+  proto.seed_lo = (uint32_t)seed; proto.seed_hi = (uint32_t)(seed >> 32);
+  proto.elem_offset = 0;
+  proto.fmt = format; proto.rnd = rounding; proto.flags = flags;
+  proto.d_amax = nullptr; proto.flt_max = 0.0f; proto.d_scale_out = nullptr;
+  k<<<h->total_cast, kThreads, 0, static_cast<cudaStream_t>(stream_)>>>(d_table, count, proto, d_scales);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int fpemu_encode_multi(const void* d_table, const void* h_table, int count, int format, int rounding, int flags,
+                                  const float* d_scales, uint64_t seed, void* stream_) {
+  if (d_table == nullptr || h_table == nullptr || count <= 0) return FPEMU_ERR_ARG;
+  const MtHeader* h = static_cast<const MtHeader*>(h_table);
+  if (h->count != count) return FPEMU_ERR_ARG;
+  if (rounding < 0 || rounding >= FPEMU_RND_COUNT) return FPEMU_ERR_MODE;
+  if (flags & FPEMU_FLAG_DAZ) return FPEMU_ERR_MODE;             // DAZ variants: use the per-tensor entry point
+  const bool scaled = d_scales != nullptr;
+  MultiCastKernel k = nullptr;
+  switch (format) {
+    case FPEMU_FMT_E5M2: k = epick_rnd<FPEMU_FMT_E5M2>(rounding, h->dtype, scaled); break;
+    case FPEMU_FMT_E4M3: k = epick_rnd<FPEMU_FMT_E4M3>(rounding, h->dtype, scaled); break;
+    case FPEMU_FMT_E3M4: k = epick_rnd<FPEMU_FMT_E3M4>(rounding, h->dtype, scaled); break;
+    default: break;                                              // only the three 8-bit formats have codes
+  }
+  if (k == nullptr) return FPEMU_ERR_MODE;
   if (h->total_cast == 0) return FPEMU_OK;
   CastArgs proto;
   proto.in = nullptr; proto.out = nullptr; proto.n = 0;

@@ -97,6 +97,11 @@ class ShardedPlan(object):
     def cast(self, mode, seed=0):
         return self.plan.cast(mode, seed=seed)
 
+    def amax_scaled_encode(self, mode, seed=0, flt_max=None):
+        """As amax_scaled_cast, for a plan whose outputs are uint8 code buffers: every rank ends up with the 8-bit
+        codes of its slabs and the same float32[T] scale vector."""
+        return self.plan.amax_scaled_encode(mode, flt_max=flt_max, seed=seed, reduce_fn=self._allreduce)
+
 
 def sharded_cast(slabs, mode, row_offsets=None, cols=None, outs=None, scale=1.0, seed=0, kernels=CudaKernels):
     """Constant-scale cast of row-sharded tensors: no communication at all."""

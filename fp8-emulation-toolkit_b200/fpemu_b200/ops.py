@@ -326,8 +326,12 @@ class MultiTensorPlan(object):
         for x, y in zip(ins, outs):
             _check_tensor(x)
             _check_tensor(y, "out")
-            if x.device != dev or x.dtype != dt or y.dtype != dt or y.numel() < x.numel():
+            if x.device != dev or x.dtype != dt or y.dtype not in (dt, torch.uint8) or y.numel() < x.numel():
                 raise ValueError("fpemu: multi-tensor lists must share device and dtype, outputs must match inputs")
+        # outputs of dtype uint8 make this a plan for `encode` (one byte code per element) instead of `cast`
+        self.packed = all(y.dtype == torch.uint8 for y in outs)
+        if not self.packed and any(y.dtype != dt for y in outs):
+            raise ValueError("fpemu: outputs must be all of the input dtype (cast) or all uint8 (encode)")
         self.ins, self.outs, self.count, self.device, self.dtype = ins, outs, len(ins), dev, dt
 
         class Desc(ctypes.Structure):
@@ -353,8 +357,40 @@ class MultiTensorPlan(object):
         L.check(st, "fpemu_amax_multi")
         return out
 
+    def _scales_ptr(self, d_scales):
+        if d_scales is None:
+            return None
+        if not (d_scales.is_cuda and d_scales.dtype == torch.float32 and d_scales.numel() >= self.count):
+            raise ValueError("fpemu: d_scales must be a float32 CUDA vector with one entry per tensor")
+        return d_scales.data_ptr()
+
+    def encode(self, mode, d_scales=None, seed=None):
+        """Round every tensor like `cast` and write one-byte codes into the plan's uint8 outputs, one launch."""
+        if not self.packed:
+            raise ValueError("fpemu: this plan's outputs are not uint8 code buffers")
+        fmt, rnd, flags = L.parse_mode(mode)
+        if rnd == L.RND_STOCHASTIC and seed is None:
+            seed = next_seed()
+        with _on_device(self.d_table):
+            st = L.lib().fpemu_encode_multi(self.d_table.data_ptr(), self.h_table.data_ptr(), self.count, fmt, rnd, flags,
+                                            self._scales_ptr(d_scales), int(seed or 0), _stream(self.d_table))
+        L.check(st, "fpemu_encode_multi(%s)" % mode)
+        return self.outs
+
+    def amax_scaled_encode(self, mode, flt_max=None, seed=None, reduce_fn=None):
+        """Per-tensor amax-scaled 8-bit codes for the whole list: amax launch -> [reduce_fn] -> scale launch ->
+        encode launch.  Returns (codes, scales); `decode(codes[t], fmt, scale=scales[t])` gives the cast's values."""
+        fmt, _, _ = L.parse_mode(mode)
+        vec = self.amax()
+        if reduce_fn is not None:
+            reduce_fn(vec)
+        scales = scale_from_amax(vec, FLT_MAX[fmt] if flt_max is None else flt_max)
+        return self.encode(mode, d_scales=scales, seed=seed), scales
+
     def cast(self, mode, d_scales=None, seed=None, unscale_fp32=False):
         """Cast every tensor in one launch; tensor t uses d_scales[t] (None: scale 1) and seed + t."""
+        if self.packed:
+            raise ValueError("fpemu: this plan's outputs are uint8 code buffers: use encode()")
         fmt, rnd, flags = L.parse_mode(mode)
         if unscale_fp32:
             flags |= L.FLAG_UNSCALE_FP32

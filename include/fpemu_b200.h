@@ -191,6 +191,12 @@ FPEMU_API int fpemu_amax_multi(const void* d_table, const void* h_table, int cou
 FPEMU_API int fpemu_cast_multi(const void* d_table, const void* h_table, int count, int format, int rounding,
                                int flags, const float* d_scales, uint64_t seed, void* stream);
 
+/* fpemu_encode for a whole list in one launch: same table, same CTA numbering and per-tensor seeds as
+ * fpemu_cast_multi, but every descriptor's `out` is a byte buffer of n codes (32-byte aligned like the rest).
+ * format must be E5M2, E4M3 or E3M4. */
+FPEMU_API int fpemu_encode_multi(const void* d_table, const void* h_table, int count, int format, int rounding, int flags,
+                       const float* d_scales, uint64_t seed, void* stream);
+
 /* Per-tensor amax-scaled cast that needs NO scratch memory from the caller and allocates none.
  * (No counterpart in the reference: its Python layer computes the maximum with torch and passes a float.)
  * Same result as fpemu_amax + fpemu_scale_from_amax + fpemu_cast with a device scalar, but the running

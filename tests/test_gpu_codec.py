@@ -157,3 +157,39 @@ def test_full_size_round_trip(F):
     q = F.cast(x, "E4M3_RNE")
     big = x.abs() >= 2.0 ** -5
     assert torch.equal(back[big].view(torch.int32), q[big].view(torch.int32))
+
+
+@pytest.mark.parametrize("mode", ["E4M3_RNE", "E5M2_STOCHASTIC", "E3M4_RTZ"])
+@pytest.mark.parametrize("dt", ["f32", "bf16"])
+def test_multi_tensor_encode_equals_per_tensor_encode(F, mode, dt):
+    sizes = [4096, 16, 70001, 8 * 256 * 2 * 3, 5, 33333, 1 << 18]
+    xs = [as_dtype(wide(n, 40 + i), dt)[1] for i, n in enumerate(sizes)]
+    codes = [torch.zeros(n + 32, dtype=torch.uint8, device="cuda")[:n] for n in sizes]
+    plan = F.MultiTensorPlan(xs, codes)
+    scales = torch.tensor([1.0, 3.7, 0.125, 94.09, 2.0, 1.0, 0.5], device="cuda")
+    plan.encode(mode, d_scales=scales, seed=900)
+    for t, x in enumerate(xs):
+        want = F.encode(x, mode, d_scale=scales[t:t + 1].clone(), seed=900 + t)
+        assert torch.equal(codes[t], want), "tensor %d of %s %s" % (t, mode, dt)
+    plan.encode(mode, seed=17)                                       # unscaled
+    for t, x in enumerate(xs):
+        assert torch.equal(codes[t], F.encode(x, mode, seed=17 + t))
+    with pytest.raises(ValueError):
+        plan.cast(mode)
+    with pytest.raises(ValueError):
+        F.MultiTensorPlan(xs).encode(mode)
+
+
+def test_multi_tensor_amax_scaled_codes_decode_to_the_amax_scaled_cast(F):
+    g = torch.Generator(device="cuda").manual_seed(8)
+    xs = [torch.randn(n, device="cuda", generator=g) * s for n, s in ((1 << 16, 0.02), (4096 * 3, 5.0), (100000, 1e-3))]
+    codes = [torch.empty(x.numel(), dtype=torch.uint8, device="cuda") for x in xs]
+    got, scales = F.MultiTensorPlan(xs, codes).amax_scaled_encode("E4M3_RNE")
+    outs = [torch.empty_like(x) for x in xs]
+    want, scales2 = F.MultiTensorPlan(xs, outs).amax_scaled_cast("E4M3_RNE")
+    assert torch.equal(scales, scales2)
+    for t, x in enumerate(xs):
+        back = F.decode(got[t], "E4M3", scale=float(scales[t]))
+        big = (x.abs() * scales[t]) >= 2.0 ** -5
+        assert torch.equal(back[big].view(torch.int32), want[t][big].view(torch.int32))
+        assert float(big.float().mean()) > 0.99

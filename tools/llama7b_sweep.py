@@ -46,6 +46,7 @@ def main():
     ap.add_argument("--reps", type=int, default=5)
     ap.add_argument("--mode", default="E4M3_RNE")
     ap.add_argument("--multi", action="store_true", help="multi-tensor launches (3 launches per sweep instead of 583)")
+    ap.add_argument("--packed", action="store_true", help="write 8-bit codes instead of de-quantised values (implies --multi)")
     args = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -69,12 +70,18 @@ def main():
         offsets.append(r0)
         cols.append(c)
         total += r * c
-    outs = [torch.empty_like(s) for s in slabs]
+    if args.packed:
+        args.multi = True
+        outs = [torch.empty(s.shape, dtype=torch.uint8, device=dev) for s in slabs]
+    else:
+        outs = [torch.empty_like(s) for s in slabs]
     local_elems = sum(s.numel() for s in slabs)
 
     plan = fd.ShardedPlan(slabs, row_offsets=offsets, cols=cols, outs=outs) if args.multi else None
 
     def run():
+        if args.packed:
+            return plan.amax_scaled_encode(args.mode, seed=7)
         if plan is not None:
             return plan.amax_scaled_cast(args.mode, seed=7)
         return fd.sharded_amax_scaled_cast(slabs, args.mode, row_offsets=offsets, cols=cols, outs=outs, seed=7)
@@ -115,8 +122,8 @@ def main():
         ar_us = a.elapsed_time(b) / 50 * 1e3
 
     if rank == 0:
-        gbs = 3.0 * esz * total / (ms * 1e-3) / 1e9
-        print(json.dumps({"workload": "llama7b per-tensor amax-scaled %s" % args.mode, "dtype": args.dtype, "n_gpus": world,
+        gbs = ((2.0 * esz + 1.0) if args.packed else 3.0 * esz) * total / (ms * 1e-3) / 1e9
+        print(json.dumps({"workload": "llama7b per-tensor amax-scaled %s%s" % (args.mode, " -> 8-bit codes" if args.packed else ""), "dtype": args.dtype, "n_gpus": world,
                           "tensors": len(shapes), "elements": total, "elements_per_rank": local_elems,
                           "ms_per_sweep_device": ms, "ms_per_sweep_wall": wall * 1e3,
                           "aggregate_GBps_algorithmic": gbs, "per_gpu_GBps": gbs / world,
