@@ -16,7 +16,7 @@ namespace fpemu {
 template <int FMT, int RND, bool DAZ, int DT, bool SCALED>
 __global__ void __launch_bounds__(kThreads) encode_vec_kernel(const CastArgs a) {
   const ScaleCtx sc = make_scale_ctx<DT, SCALED>(a);
-  encode_cta<FMT, RND, DAZ, DT, SCALED, kCodecUnroll>(a, sc, (int64_t)blockIdx.x, blockIdx.x == gridDim.x - 1);
+  encode_cta<FMT, RND, DAZ, DT, SCALED, CodecUnroll<DT>::value>(a, sc, (int64_t)blockIdx.x, blockIdx.x == gridDim.x - 1);
 }
 
 // Codes of one output vector -> values, un-scaled like the cast.
@@ -33,7 +33,7 @@ __device__ __forceinline__ void decode_vec(const uint32_t (&w)[4], const ScaleCt
 template <int FMT, int DT, bool SCALED>
 __global__ void __launch_bounds__(kThreads) decode_vec_kernel(const CastArgs a) {
   constexpr int VE = DtInfo<DT>::kVecElems;
-  constexpr int U = kCodecUnroll;
+  constexpr int U = CodecUnroll<DT>::value;
   const ScaleCtx sc = make_scale_ctx<DT, SCALED>(a);
   const int64_t nvec = a.n / VE;
   const char* in = static_cast<const char*>(a.in);
@@ -159,7 +159,7 @@ static int launch_codec(CodecKernel k, void (*generic)(const CastArgs, int), con
   if (a.n == 0) return FPEMU_OK;
   if (k != nullptr) {
     const int ve = dtype == FPEMU_DT_F32 ? 8 : 16;
-    const int64_t per_cta = (int64_t)kThreads * kCodecUnroll;
+    const int64_t per_cta = (int64_t)kThreads * (dtype == FPEMU_DT_F32 ? CodecUnroll<FPEMU_DT_F32>::value : CodecUnroll<FPEMU_DT_F16>::value);
     int64_t want = (a.n / ve + per_cta - 1) / per_cta;
     if (want < 1) want = 1;
     if (want > 0x7FFFFFFFLL) return FPEMU_ERR_TOO_LARGE;

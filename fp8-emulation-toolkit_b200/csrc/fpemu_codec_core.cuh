@@ -5,7 +5,14 @@
 
 namespace fpemu {
 
-constexpr int kCodecUnroll = 4;   // vectors in flight per thread (reads are 4/5 of the traffic)
+// Vectors in flight per thread of the single-tensor encode / decode kernels (reads are 4/5 of the encode traffic).
+#ifndef FPEMU_CODEC_U32
+#define FPEMU_CODEC_U32 4
+#endif
+#ifndef FPEMU_CODEC_U16
+#define FPEMU_CODEC_U16 4
+#endif
+template <int DT> struct CodecUnroll { static constexpr int value = (DT == FPEMU_DT_F32) ? FPEMU_CODEC_U32 : FPEMU_CODEC_U16; };
 
 __device__ __forceinline__ void stg_codes(void* p, const uint32_t (&w)[4], int words) {
   if (words == 2) asm volatile("st.global.L1::no_allocate.v2.u32 [%0], {%1,%2};" :: "l"(p), "r"(w[0]), "r"(w[1]) : "memory");
