@@ -366,13 +366,31 @@ def quantize_module_gradient(self, grad_input, grad_output):
     return grad_input
 
 
+_OUTPUT_CAST_OUT_OF_PLACE = False
+
+
+def set_output_cast_out_of_place(flag):
+    """False (default): module outputs are cast in place like the reference (`qutils.py:611`), bit-for-bit the
+    reference's behaviour on this PyTorch, including its loss of the output-gradient hook on view outputs.
+    True: while autograd is recording, outputs are cast into a new tensor (see quantize_module_output)."""
+    global _OUTPUT_CAST_OUT_OF_PLACE
+    _OUTPUT_CAST_OUT_OF_PLACE = bool(flag)
+
+
 def quantize_module_output(self, input, output):
     """Forward hook (reference :586-616): register the output-gradient hook, cast the output in place."""
     qc = self.qconfig
     if torch.is_tensor(output):
         qc.register_output_grad_hook(output)
         if qc.oact_qconfig is not None and qc.oact_qconfig.is_enabled:
-            output = quantize_tensor(output, qc.oact_qconfig, self.qparams.oact_qparams, inplace=True)
+            # The reference always casts in place.  While autograd is recording, the output of a Linear on a 3-D
+            # input is a VIEW of the 2-D addmm result; an in-place op on such a view makes autograd rebuild the graph
+            # through CopySlices (four extra full-tensor copies per module in backward, 288 per BERT-base step) and
+            # the output-gradient hook registered two lines above never fires, because the gradient no longer
+            # passes through the node it was registered on.  set_output_cast_out_of_place(True) returns a new
+            # tensor instead: same forward values, no copies, and the output-gradient hook fires.
+            inplace = not (_OUTPUT_CAST_OUT_OF_PLACE and output.requires_grad and torch.is_grad_enabled())
+            output = quantize_tensor(output, qc.oact_qconfig, self.qparams.oact_qparams, inplace=inplace)
     return output
 
 

@@ -196,6 +196,45 @@ def test_hybrid_training_step(G, mp):
     assert emu.emulator.global_steps == 1
 
 
+def test_output_cast_in_place_vs_out_of_place_under_autograd(mp):
+    """Linear on a 3-D input returns a view; the reference's in-place output cast on it makes PyTorch drop the
+    output-gradient hook (checked on the reference's own code path in this PyTorch: the hook does not fire) and adds
+    CopySlices copies.  Default = the reference's behaviour; set_output_cast_out_of_place(True) = same forward values,
+    hook fires."""
+    from mpemu import mpt_emu, qutils
+
+    def run(out_of_place):
+        qutils.set_output_cast_out_of_place(out_of_place)
+        try:
+            torch.manual_seed(0)
+            model = torch.nn.Sequential(torch.nn.Linear(64, 48), torch.nn.Linear(48, 32)).cuda()
+            model, emu = mpt_emu.initialize(model, None, training_algo="hybrid", device="cuda")
+            fired = []
+            orig = qutils.quantize_tensor
+
+            def spy(t, cfg, params, inplace=False):
+                fired.append((cfg.dtype, tuple(t.shape), inplace))
+                return orig(t, cfg, params, inplace=inplace)
+            qutils.quantize_tensor = spy
+            try:
+                x = torch.randn(4, 10, 64, device="cuda", generator=torch.Generator(device="cuda").manual_seed(1))
+                y = model(x)
+                y.float().pow(2).sum().backward()
+            finally:
+                qutils.quantize_tensor = orig
+            return y.detach().clone(), fired
+        finally:
+            qutils.set_output_cast_out_of_place(False)
+
+    y_ref, calls_ref = run(False)
+    y_new, calls_new = run(True)
+    assert torch.equal(y_ref, y_new)                                   # forward values do not depend on the switch
+    ograd = lambda calls: [c for c in calls if c[0] == "e5m2" and len(c[1]) == 3 and c[1][-1] in (48, 32) and not c[2]]
+    # out-of-place: one output-gradient cast per module (shapes 4x10x48 and 4x10x32) in addition to the input-gradient casts
+    assert len(ograd(calls_new)) > len(ograd(calls_ref))
+    assert len(calls_new) == len(calls_ref) + 2
+
+
 def test_fpemuop_autograd_contract(mp):
     """FPEmuOp: 'NONE' passes through, straight-through gradient, mark_dirty on in-place, sparse values path."""
     from mpemu.pytquant.cuda.fpemu import FPEmuOp

@@ -47,8 +47,27 @@ def kernel_time_ms(fn):
     return ours / 1e3, total / 1e3, n_ours
 
 
+def kernel_breakdown(fn, top=14):
+    """Device time by kernel name for one call: [(name, ms, launches)], longest first."""
+    from torch.profiler import ProfilerActivity, profile
+    fn()
+    torch.cuda.synchronize()
+    with profile(activities=[ProfilerActivity.CUDA]) as prof:
+        fn()
+        torch.cuda.synchronize()
+    acc = {}
+    for e in prof.events():
+        if e.device_type == torch.autograd.DeviceType.CUDA:
+            t = acc.setdefault(e.name[:90], [0.0, 0])
+            t[0] += e.device_time / 1e3
+            t[1] += 1
+    rows = sorted(((k, round(v[0], 3), v[1]) for k, v in acc.items()), key=lambda r: -r[1])
+    return rows[:top], round(sum(v[0] for v in acc.values()), 3), sum(v[1] for v in acc.values())
+
+
 def main():
     ap = argparse.ArgumentParser()
+    ap.add_argument("--breakdown", action="store_true", help="also list device time by kernel name")
     ap.add_argument("--resnet-batch", type=int, default=64)
     ap.add_argument("--bert-batch", type=int, default=12)
     ap.add_argument("--bert-seq", type=int, default=384)
@@ -88,6 +107,8 @@ def main():
         loss.backward()
         opt.step()
     base = timed(step)
+    if args.breakdown:
+        out["bert_plain_breakdown"] = kernel_breakdown(step)
     bert, emu = mpt_emu.initialize(bert, None, training_algo="hybrid", list_exempt_layers=["qa_outputs"], device="cuda")
 
     def estep():
@@ -97,6 +118,15 @@ def main():
         emu.optimizer_step(opt)
     emul = timed(estep)
     ours, total, n = kernel_time_ms(estep)
+    if args.breakdown:
+        out["bert_emulated_breakdown"] = kernel_breakdown(estep)
+    from mpemu import qutils
+    qutils.set_output_cast_out_of_place(True)
+    emul_oop = timed(estep)
+    ours_oop, total_oop, n_oop = kernel_time_ms(estep)
+    qutils.set_output_cast_out_of_place(False)
+    out["bert_base_hybrid_step_out_of_place_outputs"] = {"emulated_step_ms": emul_oop, "cast_kernel_ms_per_step": ours_oop,
+                                                         "all_kernel_ms_per_step": total_oop, "cast_launches_per_step": n_oop}
     out["bert_base_hybrid_step"] = {"batch": args.bert_batch, "seq": args.bert_seq, "fp32_step_ms": base, "emulated_step_ms": emul,
                                     "cast_kernel_ms_per_step": ours, "all_kernel_ms_per_step": total, "cast_launches_per_step": n}
     print(json.dumps(out, indent=1))
