@@ -25,6 +25,7 @@ class CudaKernels(object):
     amax = staticmethod(_ops.amax)
     scale_from_amax = staticmethod(_ops.scale_from_amax)
     cast = staticmethod(_ops.cast)
+    encode = staticmethod(_ops.encode)
 
 
 def _world(group):
@@ -70,6 +71,22 @@ def sharded_amax_scaled_cast(slabs, mode, row_offsets=None, cols=None, outs=None
         results.append(kernels.cast(x, mode, out=out, d_scale=scales[t:t + 1], seed=seed + t,
                                     elem_offset=row_offsets[t] * cols[t], unscale_fp32=unscale_fp32))
     return results, scales
+
+
+def sharded_amax_scaled_encode(slabs, mode, row_offsets=None, cols=None, outs=None, group=None, seed=0,
+                               flt_max=None, kernels=CudaKernels):
+    """As sharded_amax_scaled_cast, but every rank ends up with the 8-bit codes of its slabs (uint8) plus the common
+    float32[T] scale vector — the wire form of a row-sharded weight set.  Same single all-reduce(MAX)."""
+    fmt, _, _ = L.parse_mode(mode)
+    if flt_max is None:
+        flt_max = _ops.FLT_MAX[fmt]
+    n = len(slabs)
+    row_offsets = row_offsets or [0] * n
+    cols = cols or [(x.shape[-1] if x.dim() > 1 else 1) for x in slabs]
+    scales = kernels.scale_from_amax(global_amax(slabs, group=group, kernels=kernels), flt_max)
+    codes = [kernels.encode(x, mode, out=None if outs is None else outs[t], d_scale=scales[t:t + 1], seed=seed + t,
+                            elem_offset=row_offsets[t] * cols[t]) for t, x in enumerate(slabs)]
+    return codes, scales
 
 
 class ShardedPlan(object):

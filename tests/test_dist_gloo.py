@@ -41,6 +41,17 @@ class OracleKernels(object):
         return y
 
 
+    @staticmethod
+    def encode(x, mode, out=None, scale=1.0, d_scale=None, seed=0, elem_offset=0):
+        from oracle import fpemu_oracle as O
+        s = float(d_scale[0]) if d_scale is not None else scale
+        c = torch.from_numpy(O.encode(x.numpy(), mode, scale=s, seed=seed, elem_offset=elem_offset)).reshape(x.shape)
+        if out is not None:
+            out.copy_(c)
+            return out
+        return c
+
+
 def _tensors():
     g = torch.Generator().manual_seed(17)
     shapes = [(37, 16), (64, 48), (5, 32), (1, 16)]          # 1 row: one rank gets an empty slab
@@ -63,7 +74,11 @@ def _worker(rank, world, port, mode, q):
                                                    cols=[t.shape[1] for t in full], seed=11, kernels=OracleKernels)
         plain = fd.sharded_cast(slabs, "E5M2_STOCHASTIC", row_offsets=[b[0] for b in bounds],
                                 cols=[t.shape[1] for t in full], seed=5, kernels=OracleKernels)
-        q.put((rank, [o.numpy() for o in outs], scales.numpy(), [p.numpy() for p in plain], bounds))
+        codes, cscales = fd.sharded_amax_scaled_encode(slabs, mode, row_offsets=[b[0] for b in bounds],
+                                                       cols=[t.shape[1] for t in full], seed=11, kernels=OracleKernels)
+        assert torch.equal(cscales, scales)
+        q.put((rank, [o.numpy() for o in outs], scales.numpy(), [p.numpy() for p in plain], bounds,
+               [c.numpy() for c in codes]))
     finally:
         dist.destroy_process_group()
 
@@ -90,6 +105,8 @@ def test_two_rank_sharded_cast_equals_unsharded(mode):
         assert O.same_bits_or_both_nan(got, want).all(), "tensor %d" % t
         for r in results:
             assert r[2][t] == np.float32(s)                               # every rank derived the same scale
+        want_codes = O.encode(x.numpy().reshape(-1), mode, scale=s, seed=11 + t).reshape(x.shape)
+        assert (np.concatenate([r[5][t] for r in results], axis=0) == want_codes).all(), "codes of tensor %d" % t
         want_plain = O.cast(x.numpy().reshape(-1), "E5M2_STOCHASTIC", seed=5 + t).reshape(x.shape)
         got_plain = np.concatenate([r[3][t] for r in results], axis=0)
         assert O.same_bits_or_both_nan(got_plain, want_plain).all()
