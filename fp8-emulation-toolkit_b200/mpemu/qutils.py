@@ -262,9 +262,12 @@ def quantize_tensor(tensor, qtconfig, qtparams, inplace=False):
 
     if qtconfig.scaling is True:
         if qtconfig.scaling_method == "mean":
-            mean = torch.mean(torch.abs(tensor.detach().flatten())).item()
-            scale = _mean_scale(mean, qtconfig.get_flt_min(), 1e-5)
-            return fpemu_device_fn(tensor, mode, inplace=inplace, scale=scale)
+            # same expression as the reference (:276-281), kept on the device: no .item(), no host sync
+            flt_min = qtconfig.get_flt_min()
+            mean = torch.abs(torch.mean(torch.abs(tensor.detach().flatten())))
+            mean = torch.where(mean > 1e-5, mean, torch.full_like(mean, flt_min))
+            scale = torch.clamp(flt_min / mean, min=1.0)
+            return fpemu_device_fn(tensor, mode, inplace=inplace, scale=scale.float().reshape(1))
         if takes_scale and _supported_dtype(tensor):
             return _scaled_cast(tensor, mode, inplace, "tensor", flt_max, 0, 0, True)
         return fpemu_device_fn(tensor, mode, inplace=inplace)
