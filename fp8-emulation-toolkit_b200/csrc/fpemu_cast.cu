@@ -87,7 +87,7 @@ __global__ void __launch_bounds__(256) cast_generic_kernel(const CastArgs a, con
 }
 
 // Same rare modes, but aligned buffers: 256-bit vector I/O, one Philox draw per vector, element-wise rounding.
-// (E4M3_IEEE, FP4, RNAZ / RNTZ / RPINF / RNINF, DAZ variants without a packed kernel.)
+// (E4M3_IEEE, FP4; anything else without a packed kernel runs the fully run-time variant.)
 // CFMT / CRND >= 0 fix the format / rounding at compile time (the element-wise code then folds to a few dozen
 // instructions); -1 reads them from the arguments.
 template <int DT, int CFMT, int CRND>
@@ -189,7 +189,15 @@ static CastKernel pick_rnd(int rnd, bool daz, int dt, bool scaled) {
   if (FMT == FPEMU_FMT_E5M2 && daz) {
     if (rnd == FPEMU_RND_RNE) return pick_dt<FPEMU_FMT_E5M2, FPEMU_RND_RNE, true>(dt, scaled);
     if (rnd == FPEMU_RND_STOCHASTIC) return pick_dt<FPEMU_FMT_E5M2, FPEMU_RND_STOCHASTIC, true>(dt, scaled);
+    if (rnd == FPEMU_RND_RNAZ) return pick_dt<FPEMU_FMT_E5M2, FPEMU_RND_RNAZ, true>(dt, scaled);
+    if (rnd == FPEMU_RND_RNTZ) return pick_dt<FPEMU_FMT_E5M2, FPEMU_RND_RNTZ, true>(dt, scaled);
     return nullptr;
+  }
+  if (FMT == FPEMU_FMT_E5M2) {                    // the reference's extra E5M2 rounding modes (:1058-1158)
+    if (rnd == FPEMU_RND_RNAZ) return pick_dt<FPEMU_FMT_E5M2, FPEMU_RND_RNAZ, false>(dt, scaled);
+    if (rnd == FPEMU_RND_RNTZ) return pick_dt<FPEMU_FMT_E5M2, FPEMU_RND_RNTZ, false>(dt, scaled);
+    if (rnd == FPEMU_RND_RPINF) return pick_dt<FPEMU_FMT_E5M2, FPEMU_RND_RPINF, false>(dt, scaled);
+    if (rnd == FPEMU_RND_RNINF) return pick_dt<FPEMU_FMT_E5M2, FPEMU_RND_RNINF, false>(dt, scaled);
   }
   switch (rnd) {
     case FPEMU_RND_RNE:        return pick_dt<FMT, FPEMU_RND_RNE, false>(dt, scaled);
@@ -217,12 +225,6 @@ static CastKernel pick_generic(int fmt, int rnd, int dt) {
     if (rnd == FPEMU_RND_RTZ) return pick_generic_dt<FPEMU_FMT_E4M3_IEEE, FPEMU_RND_RTZ>(dt);
   }
   if (fmt == FPEMU_FMT_FP4) return pick_generic_dt<FPEMU_FMT_FP4, FPEMU_RND_RNE>(dt);
-  if (fmt == FPEMU_FMT_E5M2) {
-    if (rnd == FPEMU_RND_RNAZ) return pick_generic_dt<FPEMU_FMT_E5M2, FPEMU_RND_RNAZ>(dt);
-    if (rnd == FPEMU_RND_RNTZ) return pick_generic_dt<FPEMU_FMT_E5M2, FPEMU_RND_RNTZ>(dt);
-    if (rnd == FPEMU_RND_RPINF) return pick_generic_dt<FPEMU_FMT_E5M2, FPEMU_RND_RPINF>(dt);
-    if (rnd == FPEMU_RND_RNINF) return pick_generic_dt<FPEMU_FMT_E5M2, FPEMU_RND_RNINF>(dt);
-  }
   return pick_generic_dt<-1, -1>(dt);
 }
 

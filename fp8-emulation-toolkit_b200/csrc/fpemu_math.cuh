@@ -94,6 +94,16 @@ __device__ __forceinline__ uint32_t round_pair_e5m2(uint32_t h, uint32_t r2) {
       uint32_t lsb = (h >> 8) & 0x00010001u & ok;
       return (h + (0x007F007Fu & ok) + lsb) & kKeep;
     }
+    if (RND == FPEMU_RND_RNAZ || RND == FPEMU_RND_RNTZ || RND == FPEMU_RND_RPINF || RND == FPEMU_RND_RNINF) {
+      // round_up_bit(): RNAZ = dropped >= half, RNTZ = dropped > half, RPINF / RNINF = dropped >= half on positive /
+      // negative lanes only — a constant added below the kept byte, fp16 subnormals included; NaN lanes (which
+      // compare false with everything) are only masked, Inf + 0x80 stays Inf after the mask
+      const __half2 zero = as_h2(0u);
+      const uint32_t lanes = (RND == FPEMU_RND_RPINF) ? __hgt2_mask(hv, zero)
+                           : (RND == FPEMU_RND_RNINF) ? __hlt2_mask(hv, zero) : __heq2_mask(hv, hv);
+      const uint32_t inc = (RND == FPEMU_RND_RNTZ) ? 0x007F007Fu : 0x00800080u;
+      return (h + (inc & lanes)) & kKeep;
+    }
     // stochastic: fp16-normal lanes add 8 random bits, fp16-subnormal lanes round to nearest even
     uint32_t is_sub = __hlt2_mask(av, min_normal);
     uint32_t is_nrm = __hlt2_mask(av, as_h2(h2c(0x7C00))) & ~is_sub;
@@ -107,6 +117,8 @@ __device__ __forceinline__ uint32_t round_pair_e5m2(uint32_t h, uint32_t r2) {
   uint32_t inc;
   if (RND == FPEMU_RND_RNE) inc = (0x007F007Fu + ((h >> 8) & 0x00010001u)) & is_nrm;
   else if (RND == FPEMU_RND_STOCHASTIC) inc = r2 & is_nrm & __hlt2_mask(av, as_h2(h2c(0x7C00)));
+  else if (RND == FPEMU_RND_RNAZ) inc = 0x00800080u & is_nrm;
+  else if (RND == FPEMU_RND_RNTZ) inc = 0x007F007Fu & is_nrm;
   else inc = 0u;
   return (h + inc) & kKeep & ~is_sub;
 }
