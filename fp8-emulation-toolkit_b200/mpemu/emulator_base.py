@@ -163,12 +163,45 @@ class EmulatorBase(object):
         if self.using_apex and hasattr(optimizer, "_master_params_to_model_params"):
             from apex import amp
             return list(amp.master_params(optimizer))
+        # without apex: an optimizer (or wrapper) may expose its fp32 master copies itself, in named_parameters() order
+        explicit = getattr(optimizer, "fpemu_master_params", None)
+        if explicit is not None:
+            return list(explicit() if callable(explicit) else explicit)
         return None
+
+    def _cast_list_in_place(self, tensors, mode):
+        """One multi-tensor launch for a list of same-dtype CUDA tensors (the reference loops over parameters,
+        hybrid_emu.py:110-139); falls back to per-tensor calls for lists the table cannot describe."""
+        from fpemu_b200 import ops as _ops
+        from .pytquant import fpemu_cuda
+        tensors = [t for t in tensors if t.numel()]
+        if not tensors:
+            return
+        key = (mode, tuple((t.data_ptr(), t.numel(), t.dtype) for t in tensors))
+        plan = self._plans.get(key) if hasattr(self, "_plans") else None
+        if plan is None:
+            if not hasattr(self, "_plans"):
+                self._plans = {}
+            try:
+                ok = len({(t.dtype, t.device) for t in tensors}) == 1 and all(t.is_contiguous() for t in tensors)
+                plan = _ops.MultiTensorPlan(tensors) if ok else False
+            except ValueError:
+                plan = False                                   # unaligned storage offsets
+            if len(self._plans) > 8:
+                self._plans.clear()
+            self._plans[key] = plan
+        if plan is False:
+            for t in tensors:
+                t.data = fpemu_cuda.FPEmuOp.apply(t.data, mode, True)
+        else:
+            plan.cast(mode)
 
     def update_master_params(self, optimizer):
         """Re-quantize the fp32 master copy after the optimizer step: FLOAT16_STOCHASTIC (or E5M2_STOCHASTIC)
         in place, embeddings optionally to an fp8 format.  Only apex-amp optimizers keep master copies; without
         them this prints a notice and does nothing, exactly like the reference (hybrid_emu.py:175-176)."""
+        if not (self.use_fp16_master or self.use_e5m2_master):
+            return                                              # hybrid_emu.py:193-197: nothing selected, nothing done
         masters = self._master_params(optimizer)
         if masters is None:
             if not getattr(self, "_warned_master", False):
@@ -178,8 +211,12 @@ class EmulatorBase(object):
         from .pytquant import fpemu_cuda
         emb_mode = ("E5M2_STOCHASTIC" if self.use_e5m2_emb else "E4M3_STOCHASTIC" if self.use_e4m3_emb
                     else "E3M4_STOCHASTIC" if self.use_e3m4_emb else None)
+        plain = []
         for param, (name, _) in zip(masters, self.model.named_parameters()):
             if not param.is_cuda:
+                continue
+            if not (emb_mode is not None and "embeddings" in name) and (self.use_fp16_master or self.use_e5m2_master):
+                plain.append(param.data)
                 continue
             if emb_mode is not None and "embeddings" in name:
                 param.data = fpemu_cuda.FPEmuOp.apply(param.data, "FLOAT16_STOCHASTIC", True)
@@ -189,10 +226,8 @@ class EmulatorBase(object):
                     param.data = fpemu_cuda.FPEmuOp.apply(param.data, emb_mode, True, 1.0, True, param.size()[1])
                 else:
                     param.data = fpemu_cuda.FPEmuOp.apply(param.data, emb_mode, True)
-            elif self.use_fp16_master:
-                param.data = fpemu_cuda.FPEmuOp.apply(param.data, "FLOAT16_STOCHASTIC", True)
-            elif self.use_e5m2_master:
-                param.data = fpemu_cuda.FPEmuOp.apply(param.data, "E5M2_STOCHASTIC", True)
+        if plain:
+            self._cast_list_in_place(plain, "FLOAT16_STOCHASTIC" if self.use_fp16_master else "E5M2_STOCHASTIC")
 
     def optimizer_step(self, optimizer):
         optimizer.step()

@@ -235,6 +235,42 @@ def test_output_cast_in_place_vs_out_of_place_under_autograd(mp):
     assert len(calls_new) == len(calls_ref) + 2
 
 
+def test_master_parameter_requantization_is_one_multi_tensor_launch(mp):
+    """hybrid_emu.py:110-139 loops over the fp32 master parameters with one FLOAT16_STOCHASTIC op call each; here
+    the list is cast by ONE multi-tensor launch.  apex is not installed, so the masters are handed over through the
+    optimizer attribute `fpemu_master_params`."""
+    from mpemu import mpt_emu
+    import fpemu_b200
+    torch.manual_seed(0)
+    model = torch.nn.Sequential(torch.nn.Linear(96, 64), torch.nn.ReLU(), torch.nn.Linear(64, 33)).cuda().train()
+    opt = torch.optim.SGD(model.parameters(), lr=0.05)
+    model, emu = mpt_emu.initialize(model, None, training_algo="hybrid", device="cuda")
+    emu.set_master_param_precision("fp16")
+    opt.fpemu_master_params = lambda: [p for p in model.parameters()]
+    calls = []
+    orig = fpemu_b200.ops.MultiTensorPlan.cast
+
+    def spy(self, mode, *a, **k):
+        calls.append((mode, self.count))
+        return orig(self, mode, *a, **k)
+    fpemu_b200.ops.MultiTensorPlan.cast = spy
+    try:
+        for _ in range(2):
+            x = torch.randn(16, 96, device="cuda")
+            opt.zero_grad()
+            model(x).pow(2).mean().backward()
+            opt.step()
+            before = [p.detach().clone() for p in model.parameters()]
+            emu.emulator.update_master_params(opt)
+            for b, p in zip(before, model.parameters()):
+                assert torch.equal(p.detach().half().float(), p.detach())              # fp16-representable now
+                ulp = torch.maximum(b.abs(), torch.tensor(2.0 ** -14, device="cuda")) * 2.0 ** -10
+                assert bool(((p.detach() - b).abs() <= ulp).all())                     # moved by less than one fp16 ulp
+    finally:
+        fpemu_b200.ops.MultiTensorPlan.cast = orig
+    assert calls == [("FLOAT16_STOCHASTIC", 4), ("FLOAT16_STOCHASTIC", 4)]              # one launch per step, 4 tensors
+
+
 def test_fpemuop_autograd_contract(mp):
     """FPEmuOp: 'NONE' passes through, straight-through gradient, mark_dirty on in-place, sparse values path."""
     from mpemu.pytquant.cuda.fpemu import FPEmuOp
