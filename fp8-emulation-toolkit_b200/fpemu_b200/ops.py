@@ -213,21 +213,34 @@ def scale_from_amax(d_amax, flt_max, out=None):
 _work_cache = {}
 
 
+_work_floats = None
+
+
+def _work_size():
+    global _work_floats
+    if _work_floats is None:
+        _work_floats = int(L.lib().fpemu_fused_work_floats())
+    return _work_floats
+
+
 def _work_for(x, stream):
-    """Two device floats (running maximum, scale) per (device, stream): calls on one stream execute in order, so they
-    can share the scratch; a caller that wants to keep the scale gets a fresh pair instead."""
+    """Scratch floats (running maximum, scale, per-CTA maxima of the single-launch path) per (device, stream): calls
+    on one stream execute in order, so they can share the scratch; a caller that wants to keep the scale gets a
+    fresh buffer instead."""
     key = (x.device.index, stream)
     w = _work_cache.get(key)
     if w is None:
-        w = torch.zeros(2, dtype=torch.float32, device=x.device)
+        w = torch.zeros(_work_size(), dtype=torch.float32, device=x.device)
         _work_cache[key] = w
     return w
 
 
 def cast_amax_scaled(x, mode, out=None, flt_max=None, seed=None, elem_offset=0, unscale_fp32=False,
-                     d_amax=None, return_scale=False):
+                     d_amax=None, return_scale=False, fused=True):
     """Per-tensor amax-scaled cast without a host sync (the `per-tensor` / `max` branch of quantize_tensor,
-    qutils.py:274-287).  One library call: memset + amax kernel + cast kernel on the current stream.
+    qutils.py:274-287).  One library call: a single cooperative launch for tensors that fit in registers (about
+    4.8 M fp32 elements), else memset + amax kernel + cast kernel, on the current stream; `fused=False` forces the
+    three-launch path (same results).
     `d_amax` lets a caller supply an already reduced (e.g. all-reduced across ranks) amax; then only the scale
     and cast kernels run."""
     fmt, rnd, flags = L.parse_mode(mode)
@@ -249,10 +262,15 @@ def cast_amax_scaled(x, mode, out=None, flt_max=None, seed=None, elem_offset=0, 
     if rnd == L.RND_STOCHASTIC and seed is None:
         seed = next_seed()
     stream = _stream(x)
-    work = torch.zeros(2, dtype=torch.float32, device=x.device) if return_scale else _work_for(x, stream)
+    work = torch.empty(_work_size(), dtype=torch.float32, device=x.device) if return_scale else _work_for(x, stream)
     with _on_device(x):
-        st = L.lib().fpemu_cast_amax_scaled(x.data_ptr(), out.data_ptr(), x.numel(), _dt(x), fmt, rnd, flags,
-                                            float(flt_max), work.data_ptr(), int(seed or 0), int(elem_offset), stream)
+        if fused:
+            st = L.lib().fpemu_cast_amax_scaled_fused(x.data_ptr(), out.data_ptr(), x.numel(), _dt(x), fmt, rnd, flags,
+                                                      float(flt_max), work.data_ptr(), work.numel(), int(seed or 0),
+                                                      int(elem_offset), stream)
+        else:
+            st = L.lib().fpemu_cast_amax_scaled(x.data_ptr(), out.data_ptr(), x.numel(), _dt(x), fmt, rnd, flags,
+                                                float(flt_max), work.data_ptr(), int(seed or 0), int(elem_offset), stream)
     L.check(st, "fpemu_cast_amax_scaled(%s)" % mode)
     return (out, work[1:2]) if return_scale else out
 

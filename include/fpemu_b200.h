@@ -132,6 +132,20 @@ FPEMU_API int fpemu_cast_amax_scaled(const void* in, void* out, int64_t n, int d
                                      int flags, float flt_max, float* d_work, uint64_t seed, uint64_t elem_offset,
                                      void* stream);
 
+/* The same cast, one enqueue when the tensor is small enough to stay in registers: a cooperative launch whose
+ * threads keep their share of the tensor across a grid-wide barrier (read once: 8 B/elem fp32 instead of 12, no
+ * memset, no atomics).  Eligible: E5M2 / E4M3 / E3M4 with RNE / STOCHASTIC / RTZ, 32-byte aligned buffers,
+ * elem_offset % 16 == 0 for stochastic rounding, and n up to (resident threads x 4 vectors) — about 4.8 M float32 or
+ * 9.7 M 16-bit elements on a B200; everything else silently takes fpemu_cast_amax_scaled's three-launch path, so
+ * the results never depend on which path ran.  d_work: work_floats device floats, at least 2; the single-launch
+ * path needs 2 + its grid size (fpemu_fused_work_floats() is always enough).  d_work[0] = amax and d_work[1] = scale
+ * on return, as above.  This is the call the module hooks make thousands of times per training step
+ * (mpemu/qutils.py:274-287 from :478-616). */
+FPEMU_API int fpemu_fused_work_floats(void);
+FPEMU_API int fpemu_cast_amax_scaled_fused(const void* in, void* out, int64_t n, int dtype, int format, int rounding,
+                                 int flags, float flt_max, float* d_work, int work_floats, uint64_t seed,
+                                 uint64_t elem_offset, void* stream);
+
 /* Row-wise (per-channel) amax-scaled cast of a rows x cols row-major matrix: each row gets
  * scale = clamp(flt_max / max|row|).  One launch replaces the Python per-channel loop of
  * mpemu/qutils.py:289-311.  d_row_scale (optional, rows floats) receives the scales used. */

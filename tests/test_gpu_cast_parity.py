@@ -543,3 +543,47 @@ def test_blocked_with_one_block_spanning_a_large_tensor(F, mode, dt):
     import fpemu_cuda
     y = fpemu_cuda.forward(dev(x), mode, x.size, False, 1.0, True, x.size)[0]
     assert_same(host(y), got, "through fpemu_cuda.forward")
+
+
+@pytest.mark.parametrize("mode", ["E4M3_RNE", "E5M2_STOCHASTIC", "E3M4_RTZ", "E4M3_STOCHASTIC"])
+@pytest.mark.parametrize("dt", ["f32", "f16", "bf16"])
+def test_single_launch_amax_scaled_cast_equals_the_three_launch_path(F, mode, dt):
+    """fpemu_cast_amax_scaled_fused: one cooperative launch for tensors that fit in registers, the three-launch path
+    above that; the result must not depend on which one ran (sizes straddle the capacity of about 4.8 M fp32
+    elements), must match the oracle, and amax / scale must come back in the work buffer."""
+    tdt = {"f32": torch.float32, "f16": torch.float16, "bf16": torch.bfloat16}[dt]
+    g = torch.Generator(device="cuda").manual_seed(12)
+    for n in (1, 7, 8, 4097, 65536 + 3, 768 * 768, 12 * 384 * 768, 4849664, 4849664 + 8, 9699328, 9699328 + 16, 11000000):
+        x = (torch.randn(n, device="cuda", generator=g) * 0.37).to(tdt)
+        a, sa = F.cast_amax_scaled(x, mode, seed=5, return_scale=True, fused=True)
+        b, sb = F.cast_amax_scaled(x, mode, seed=5, return_scale=True, fused=False)
+        bits = torch.int32 if dt == "f32" else torch.int16
+        assert torch.equal(a.view(bits), b.view(bits)), "%s %s n=%d" % (mode, dt, n)
+        assert torch.equal(sa, sb)
+        y = x.clone()
+        F.cast_amax_scaled(y, mode, out=y, seed=5)                                   # in place
+        assert torch.equal(y.view(bits), b.view(bits))
+    x = dev(wide(300001, 77) * np.float32(1e-3))
+    got = host(F.cast_amax_scaled(x, "E4M3_RNE"))
+    xn = host(x)
+    s = O.scale_from_amax(O.amax(xn), 448.0)
+    assert_same(got, O.cast(xn, "E4M3_RNE", scale=s), "fused vs oracle")
+
+
+def test_single_launch_amax_scaled_cast_in_a_cuda_graph(F):
+    x = torch.randn(1 << 20, device="cuda")
+    y = torch.empty_like(x)
+    want = F.cast_amax_scaled(x, "E4M3_RNE", fused=False)
+    s = torch.cuda.Stream()
+    with torch.cuda.stream(s):
+        F.cast_amax_scaled(x, "E4M3_RNE", out=y)                                     # warm-up on the capture stream
+        s.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, stream=s):
+            F.cast_amax_scaled(x, "E4M3_RNE", out=y)
+    y.zero_()
+    x.mul_(3.0)
+    want = F.cast_amax_scaled(x, "E4M3_RNE", fused=False)
+    graph.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(y.view(torch.int32), want.view(torch.int32))
