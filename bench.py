@@ -319,9 +319,11 @@ def run_ours(args):
     dom_ms = per_mode[dominant]
     achieved = 8.0 * n / (dom_ms * 1e-3) / 1e9
     detail = {m: {"ms": round(per_mode[m], 4), "GB/s": round(8.0 * n / (per_mode[m] * 1e-3) / 1e9, 1),
+                  "Gelem/s": round(n / (per_mode[m] * 1e-3) / 1e9, 1),
                   "frac_of_peak": round(8.0 * n / (per_mode[m] * 1e-3) / 1e9 / peak, 4)} for m in SWEEP}
     detail["E4M3_RNE_amax_scaled"] = {"ms": round(amax_scaled_ms, 4),
                                       "GB/s": round(12.0 * n / (amax_scaled_ms * 1e-3) / 1e9, 1),
+                                      "Gelem/s": round(n / (amax_scaled_ms * 1e-3) / 1e9, 1),
                                       "frac_of_peak": round(12.0 * n / (amax_scaled_ms * 1e-3) / 1e9 / peak, 4)}
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
