@@ -219,11 +219,6 @@ static CastKernel pick_generic_dt(int dt) {
 // Compile-time specialisations for the rare modes of the reference's grammar; anything else runs the
 // fully run-time variant.
 static CastKernel pick_generic(int fmt, int rnd, int dt) {
-  if (fmt == FPEMU_FMT_E4M3_IEEE) {
-    if (rnd == FPEMU_RND_RNE) return pick_generic_dt<FPEMU_FMT_E4M3_IEEE, FPEMU_RND_RNE>(dt);
-    if (rnd == FPEMU_RND_STOCHASTIC) return pick_generic_dt<FPEMU_FMT_E4M3_IEEE, FPEMU_RND_STOCHASTIC>(dt);
-    if (rnd == FPEMU_RND_RTZ) return pick_generic_dt<FPEMU_FMT_E4M3_IEEE, FPEMU_RND_RTZ>(dt);
-  }
   if (fmt == FPEMU_FMT_FP4) return pick_generic_dt<FPEMU_FMT_FP4, FPEMU_RND_RNE>(dt);
   return pick_generic_dt<-1, -1>(dt);
 }
@@ -235,7 +230,8 @@ static CastKernel pick_kernel(int fmt, int rnd, bool daz, int dt, bool scaled) {
     case FPEMU_FMT_E3M4: return pick_rnd<FPEMU_FMT_E3M4>(rnd, daz, dt, scaled);
     case FPEMU_FMT_BF16: return pick_rnd<FPEMU_FMT_BF16>(rnd, false, dt, false);
     case FPEMU_FMT_FP16: return pick_rnd<FPEMU_FMT_FP16>(rnd, false, dt, false);
-    default:             return nullptr;   // E4M3_IEEE, FP4: generic kernel
+    case FPEMU_FMT_E4M3_IEEE: return daz ? nullptr : pick_rnd<FPEMU_FMT_E4M3_IEEE>(rnd, false, dt, scaled);
+    default:             return nullptr;   // FP4 and anything without a packed kernel: generic kernel
   }
 }
 

@@ -104,7 +104,8 @@ __device__ __forceinline__ void vec_rand_bytes(const CastArgs& a, uint64_t g0, u
   rw[0] = rw[1] = rw[2] = rw[3] = 0u;
   if (RND == FPEMU_RND_STOCHASTIC) {
     const uint4 r = philox4x32_10(a.seed_lo, a.seed_hi, g0 >> 4);
-    const uint32_t m = (FMT == FPEMU_FMT_E5M2) ? 0xFFFFFFFFu : (FMT == FPEMU_FMT_E4M3 ? 0x7F7F7F7Fu : 0x3F3F3F3Fu);
+    const uint32_t m = (FMT == FPEMU_FMT_E5M2) ? 0xFFFFFFFFu
+                     : ((FMT == FPEMU_FMT_E4M3 || FMT == FPEMU_FMT_E4M3_IEEE) ? 0x7F7F7F7Fu : 0x3F3F3F3Fu);
     if (DT == FPEMU_DT_F32) {                       // 8 elements: half of the 16-byte draw
       const bool hi = (g0 >> 3) & 1u;
       rw[0] = (hi ? r.z : r.x) & m; rw[1] = (hi ? r.w : r.y) & m;
@@ -153,7 +154,7 @@ __device__ __forceinline__ void process_vec(Vec32& v, const ScaleCtx& sc, const 
   constexpr int kPairs = DtInfo<DT>::kVecElems / 2;
   constexpr bool kSR = (RND == FPEMU_RND_STOCHASTIC);
 
-  if (FMT == FPEMU_FMT_E5M2 || FMT == FPEMU_FMT_E4M3 || FMT == FPEMU_FMT_E3M4) {
+  if (FMT == FPEMU_FMT_E5M2 || FMT == FPEMU_FMT_E4M3 || FMT == FPEMU_FMT_E3M4 || FMT == FPEMU_FMT_E4M3_IEEE) {
     uint32_t rw[4];
     vec_rand_bytes<FMT, RND, DT>(a, g0, rw);
 #pragma unroll

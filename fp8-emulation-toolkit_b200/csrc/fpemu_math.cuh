@@ -170,6 +170,33 @@ __device__ __forceinline__ uint32_t round_pair_e4m3_like(uint32_t h, uint32_t r2
   return as_u32(__hmul2(as_h2(r), keepf));
 }
 
+// E4M3_IEEE (fpemu_kernels.cu:656-767): E4M3's flush and pseudo-subnormal handling, but |h| >= 256 (NaN included)
+// becomes +-Inf instead of saturating, and the rounding increment is only applied below 15.0 (`can_round`): larger
+// magnitudes are truncated.  Same p = 2^(G-e) machinery as round_pair_e4m3_like, no clamp; lanes at or above 256
+// compute garbage that the final select replaces.
+template <int RND>
+__device__ __forceinline__ uint32_t round_pair_e4m3_ieee(uint32_t h, uint32_t r2) {
+  const __half2 av = as_h2(h & kAbs2);
+  const uint32_t big = ~__hlt2_mask(av, as_h2(0x5C005C00u));                    // >= 256, or NaN
+  const uint32_t rounds = __hlt2_mask(av, as_h2(0x4B804B80u));                   // < 15.0
+  const __half2 p = as_h2(0x60006000u - (h & 0x7C007C00u));                     // 2^(9 - e) per lane
+  const __half2 keepf = __hfma2_sat(p, as_h2(0xBC00BC00u), as_h2(0x48804880u)); // 1.0 keep, 0.0 flush (|h| < 2^-9)
+  uint32_t r;
+  if (RND == FPEMU_RND_RTZ) {
+    r = h & 0xFF80FF80u;
+  } else {
+    const __half2 m = __hfma2_relu(p, as_h2(0x3C003C00u), as_h2(0xBC00BC00u));  // 2^d - 1
+    const uint32_t q = as_u32(__hadd2(m, as_h2(0x64006400u)));
+    const uint32_t ac = h & ~(q ^ 0x64006400u);                                 // clear the low d bits
+    uint32_t inc;
+    if (RND == FPEMU_RND_RNE) inc = 0x003F003Fu + (__umulhi(ac, 1u << 25) & 0x00010001u);
+    else inc = r2;
+    r = (ac + (inc & rounds)) & 0xFF80FF80u;
+  }
+  r = as_u32(__hmul2(as_h2(r), keepf));
+  return (r & ~big) | (((h & kSign2) | 0x7C007C00u) & big);
+}
+
 __device__ __forceinline__ uint32_t bf16x2_nan_lanes(uint32_t r) {
   const __nv_bfloat162 v = *reinterpret_cast<__nv_bfloat162*>(&r);
   return __hneu2_mask(v, v);
@@ -204,6 +231,7 @@ __device__ __forceinline__ uint32_t round_pair_bf16(float x0, float x1, uint32_t
 template <int FMT, int RND, bool DAZ>
 __device__ __forceinline__ uint32_t round_pair(uint32_t h, uint32_t r2) {
   if (FMT == FPEMU_FMT_E5M2) return round_pair_e5m2<RND, DAZ>(h, r2);
+  if (FMT == FPEMU_FMT_E4M3_IEEE) return round_pair_e4m3_ieee<RND>(h, r2);
   return round_pair_e4m3_like<FMT, RND>(h, r2);
 }
 
@@ -340,18 +368,20 @@ __device__ __forceinline__ uint32_t round_one_fp16(float x, int rnd, bool daz, b
   return (sign16 | (m >> 13)) & 0xFFFFu;
 }
 
-// FP4 "nearest" on an fp32 value (fpemu_kernels.cu:1002-1023): powers of 4, 1.6x round-up trick.
+// FP4 "nearest" on an fp32 value (fpemu_kernels.cu:1002-1023): powers of 4 between 4^-6 and 1, everything above
+// 1 becomes 1, everything below 2^-12 becomes +0.  The reference bumps odd negative exponents with `inval * 1.6`
+// in double precision and masks the mantissa away; only the exponent of that product survives, and it is e + 1
+// exactly when the mantissa is >= 1.25 (1.25 * 1.6 = 2; rounding cannot reach 2.0 from 1.25 - 2^-23), so the whole
+// function is integer arithmetic on the exponent field f = e + 127 ("e < 0 and odd" <=> f < 127 and f even).
 __device__ __forceinline__ float round_one_fp4(float v) {
-  uint32_t u = __float_as_uint(v);
-  int e = (int)((u >> 23) & 0xFFu) - 127;
+  const uint32_t u = __float_as_uint(v);
   const uint32_t sign = u & 0x80000000u;
-  if (e < 0 && (e % 2)) u = __float_as_uint((float)((double)v * 1.6));
-  if (e > 0) u = sign | (127u << 23);
-  u &= 0xFF800000u;
-  e = (int)((u >> 23) & 0xFFu) - 127;
-  if (e < 0 && (e % 2)) u = sign | ((uint32_t)(e + 126) << 23);
-  if (e < -12) u = 0u;
-  return __uint_as_float(u);
+  uint32_t f = (u >> 23) & 0xFFu;
+  if (f > 127u) f = 127u;                                                        // e > 0 (Inf / NaN included): 1.0
+  else if (f < 127u && !(f & 1u) && (u & 0x7FFFFFu) >= 0x200000u) f += 1u;       // 1.6x bump of an odd exponent
+  if (f < 115u) return 0.0f;                                                     // e < -12 (tested before the step below)
+  if (f < 127u && !(f & 1u)) f -= 1u;                                            // still odd: down to the even exponent
+  return __uint_as_float(sign | (f << 23));
 }
 
 // Full QDQ of one fp32 value (already widened from the tensor's dtype).  `scale`/`rscale` are what the
