@@ -98,3 +98,14 @@ def test_beyond_4Gi_elements_64bit_indexing(F, mode):
         assert O.same_bits_or_both_nan(got, want).all(), "window at %d" % start
     a = F.amax(x).item()
     assert a == x[: 1 << 28].float().abs().max().item() or a >= x[: 1 << 28].float().abs().max().item()
+    # the 8-bit wire form over the same tensor: codes and their decoded values in the same windows
+    del q
+    codes = F.encode(x, mode, seed=5)
+    back = F.decode(codes, mode.split("_")[0], dtype=torch.bfloat16)
+    for start in (0, (1 << 31) - 1000, (1 << 32) - 1000, n - 2000):
+        stop = min(n, start + 2000)
+        xs = x[start:stop].view(torch.int16).cpu().numpy().view(np.uint16)
+        want = O.encode(xs, mode, seed=5, elem_offset=start)
+        assert (codes[start:stop].cpu().numpy() == want).all(), "codes, window at %d" % start
+        got = back[start:stop].view(torch.int16).cpu().numpy().view(np.uint16)
+        assert (got == O.decode(want, mode.split("_")[0], dtype=np.uint16)).all(), "decode, window at %d" % start
