@@ -198,8 +198,9 @@ extern "C" int fpemu_cast_amax_scaled_fused(const void* in, void* out, int64_t n
       void* args[] = {(void*)&a, (void*)&d_work};
       cudaError_t err = cudaLaunchCooperativeKernel((const void*)k, dim3((unsigned)ctas), dim3(kThreads), args, 0,
                                                     static_cast<cudaStream_t>(stream_));
-      return (int)err;
-    }
+      if (err != cudaErrorCooperativeLaunchTooLarge && err != cudaErrorNotSupported) return (int)err;
+      cudaGetLastError();                  // fewer SMs available than the device reports (MPS limits, green contexts):
+    }                                      // nothing was enqueued, take the three-launch path below
   }
   return fpemu_cast_amax_scaled(in, out, n, dtype, format, rounding, flags, flt_max, d_work, seed, elem_offset, stream_);
 }
