@@ -138,6 +138,30 @@ class ClockSampler(object):
 
 
 # ---------------------------------------------------------------------------------------------- reference arm
+def bind_thread_near_gpu(index):
+    """Restrict the calling thread to the CPUs NVML reports as local to GPU `index` (its NUMA node).  Returns
+    (previous affinity or None when nothing was changed, number of CPUs now allowed)."""
+    if os.environ.get("FPEMU_BENCH_NO_AFFINITY"):
+        return None, len(os.sched_getaffinity(0))
+    try:
+        import pynvml
+        import torch
+        pynvml.nvmlInit()
+        try:
+            h = pynvml.nvmlDeviceGetHandleByUUID("GPU-" + str(torch.cuda.get_device_properties(index).uuid))
+        except Exception:
+            h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        saved = os.sched_getaffinity(0)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (max(saved) // 64) + 1)
+        cpus = {64 * w + b for w, word in enumerate(words) for b in range(64) if (int(word) >> b) & 1} & saved
+        if not cpus or cpus == saved:
+            return None, len(saved)
+        os.sched_setaffinity(0, cpus)
+        return saved, len(cpus)
+    except Exception:
+        return None, len(os.sched_getaffinity(0))
+
+
 def time_reference_cpu(n_elems, steps, warmup, modes):
     """Seconds per sweep of the reference CPU op over `modes` on an n_elems fp32 tensor, all host threads."""
     import torch
@@ -275,6 +299,9 @@ def run_ours(args):
     e2e = None
     if not args.no_e2e:
         ne = min(args.e2e_elems, n)
+        # pinned buffers are placed by first touch: run this thread on the CPUs next to this rank's GPU while they
+        # are allocated and used, so that on a multi-socket box the DMA traffic does not cross the socket link
+        saved_affinity, near = bind_thread_near_gpu(local)
         h_in = torch.randn(ne, dtype=torch.float32).pin_memory()
         h_out = torch.empty(ne, dtype=torch.float32).pin_memory()
         caster = F.HostCaster(torch.float32, chunk_elems=1 << 24, device=local)
@@ -307,7 +334,11 @@ def run_ours(args):
         e2e = {"value": e2e_bytes / dt / 1e9, "unit": UNIT,
                "h2d_bytes_per_step": int(4 * ne * (len(SWEEP) + 1)), "d2h_bytes_per_step": int(4 * ne * (len(SWEEP) + 1)),
                "elems_per_tensor": ne, "steps": e2e_steps,
-               "api": "fpemu_cast_host (C ABI, pinned host in/out, 2 x 64 MiB device staging, 3 streams)"}
+               "api": "fpemu_cast_host (C ABI, pinned host in/out, 2 x 64 MiB device staging, 3 streams)",
+               "host_cpus_near_gpu": near}
+        del h_in, h_out
+        if saved_affinity is not None:
+            os.sched_setaffinity(0, saved_affinity)
 
     if rank != 0:
         if world > 1:
