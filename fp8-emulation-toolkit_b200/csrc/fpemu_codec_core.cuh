@@ -27,11 +27,44 @@ __device__ __forceinline__ void ldg_codes(const void* p, uint32_t (&w)[4], int w
   }
 }
 
+// fp16x2 -> two E4M3 codes with the hardware conversion (F2FP.SATFINITE.E4M3.F16): round to nearest even at 3
+// mantissa bits, saturate at 448.  For |h| >= 2^-6 (the format's normal range) and for zeros this is bit for bit the
+// reference's E4M3 RNE followed by the code extraction: same rounding position, Inf and overflow -> 0x7E.  It differs
+// where the reference does: NaN (hardware 0x7F, reference 448 = 0x7E) and 0 < |h| < 2^-6 (hardware rounds once onto the
+// subnormal grid; the reference flushes below 2^-9 and rounds its pseudo-subnormals twice).  Those lanes are
+// reported in `other` and their vector is redone with the exact sequence.
+__device__ __forceinline__ uint32_t cvt_e4m3x2_rn(uint32_t h2) {
+  unsigned short r;
+  asm("cvt.rn.satfinite.e4m3x2.f16x2 %0, %1;" : "=h"(r) : "r"(h2));
+  return r;
+}
+
 // One input vector -> its codes, 4 per word.  `rw` = the vector's random bytes (vec_rand_bytes layout).
 template <int FMT, int RND, bool DAZ, int DT, bool SCALED>
-__device__ __forceinline__ void encode_vec(const Vec32& v, const ScaleCtx& sc, const uint32_t (&rw)[4], uint32_t (&w)[4]) {
+__device__ __forceinline__ void encode_vec(const Vec32& v, const ScaleCtx& sc, const uint32_t (&rw)[4], uint32_t (&w)[4],
+                                           const bool expect_normals) {
   constexpr int kPairs = DtInfo<DT>::kVecElems / 2;
   constexpr bool kSR = (RND == FPEMU_RND_STOCHASTIC);
+  // The hardware path pays off only when almost no warp meets a lane below the smallest normal (a thread that does
+  // redoes its vector, and its whole warp waits): the caller says so with FPEMU_FLAG_EXPECT_NORMALS, typically
+  // because the scale was derived from the tensor's maximum.  The codes are the same either way.
+  if (FMT == FPEMU_FMT_E4M3 && RND == FPEMU_RND_RNE && expect_normals) {
+    uint32_t other = 0u, c[kPairs];
+#pragma unroll
+    for (int k = 0; k < kPairs; ++k) {
+      const uint32_t h = pair_to_h<DT, SCALED>(v, k, sc);
+      const __half2 av = __habs2(as_h2(h));
+      // (|h| < 2^-6 or NaN) and not zero
+      other |= __hltu2_mask(av, as_h2(0x24002400u)) & __hneu2_mask(av, as_h2(0u));
+      c[k] = cvt_e4m3x2_rn(h);
+    }
+    if (other == 0u) {
+      w[0] = w[1] = w[2] = w[3] = 0u;
+#pragma unroll
+      for (int k = 0; k < kPairs; k += 2) w[k >> 1] = c[k] | (c[k + 1] << 16);
+      return;
+    }
+  }
   uint32_t e[kPairs];
 #pragma unroll
   for (int k = 0; k < kPairs; ++k) {
@@ -54,6 +87,7 @@ __device__ __forceinline__ void encode_cta(const CastArgs& a, const ScaleCtx& sc
   const char* in = static_cast<const char*>(a.in);
   char* out = static_cast<char*>(a.out);
   const int64_t base = local_cta * (kThreads * U) + threadIdx.x;
+  const bool expect_normals = (a.flags & FPEMU_FLAG_EXPECT_NORMALS) != 0;
   Vec32 v[U];
 #pragma unroll
   for (int j = 0; j < U; ++j) {
@@ -90,7 +124,7 @@ __device__ __forceinline__ void encode_cta(const CastArgs& a, const ScaleCtx& sc
     const int64_t vi = base + j * kThreads;
     if (vi < nvec) {
       uint32_t w[4];
-      encode_vec<FMT, RND, DAZ, DT, SCALED>(v[j], sc, rw[j], w);
+      encode_vec<FMT, RND, DAZ, DT, SCALED>(v[j], sc, rw[j], w, expect_normals);
       stg_codes(out + vi * VE, w, VE / 4);
     }
   }
@@ -110,7 +144,7 @@ __device__ __forceinline__ void encode_cta(const CastArgs& a, const ScaleCtx& sc
     }
     uint32_t w[4], rt[4];
     vec_rand_bytes<FMT, RND, DT>(a, a.elem_offset + (uint64_t)e0, rt);
-    encode_vec<FMT, RND, DAZ, DT, SCALED>(t, sc, rt, w);
+    encode_vec<FMT, RND, DAZ, DT, SCALED>(t, sc, rt, w, expect_normals);
     unsigned char* c = reinterpret_cast<unsigned char*>(a.out) + e0;
     for (int i = 0; i < tail; ++i) c[i] = (unsigned char)(w[i >> 2] >> ((i & 3) * 8));
   }

@@ -11,7 +11,7 @@ LIB_PATH = os.path.join(os.path.dirname(_HERE), "libfpemu_b200.so")
 # numeric values of include/fpemu_b200.h
 FMT_E5M2, FMT_E4M3, FMT_E3M4, FMT_BF16, FMT_FP16, FMT_E4M3_IEEE, FMT_FP4 = range(7)
 RND_RTZ, RND_RNE, RND_STOCHASTIC, RND_RNAZ, RND_RNTZ, RND_RPINF, RND_RNINF = range(7)
-FLAG_DAZ, FLAG_UNSCALE_FP32, FLAG_NO_SCALE_CLAMP = 1, 2, 4
+FLAG_DAZ, FLAG_UNSCALE_FP32, FLAG_NO_SCALE_CLAMP, FLAG_EXPECT_NORMALS = 1, 2, 4, 8
 DT_F32, DT_F16, DT_BF16 = range(3)
 ERR_MODE, ERR_DTYPE, ERR_SCALE, ERR_ARG, ERR_ALIGN, ERR_TOO_LARGE = -1, -2, -3, -4, -5, -6
 

@@ -85,7 +85,7 @@ def sharded_amax_scaled_encode(slabs, mode, row_offsets=None, cols=None, outs=No
     cols = cols or [(x.shape[-1] if x.dim() > 1 else 1) for x in slabs]
     scales = kernels.scale_from_amax(global_amax(slabs, group=group, kernels=kernels), flt_max)
     codes = [kernels.encode(x, mode, out=None if outs is None else outs[t], d_scale=scales[t:t + 1], seed=seed + t,
-                            elem_offset=row_offsets[t] * cols[t]) for t, x in enumerate(slabs)]
+                            elem_offset=row_offsets[t] * cols[t], expect_normals=True) for t, x in enumerate(slabs)]
     return codes, scales
 
 

@@ -105,11 +105,14 @@ def _d_scale_ptr(d_scale):
     return d_scale.data_ptr()
 
 
-def encode(x, mode, out=None, scale=1.0, d_scale=None, seed=None, elem_offset=0, n=None):
+def encode(x, mode, out=None, scale=1.0, d_scale=None, seed=None, elem_offset=0, n=None, expect_normals=False):
     """Round `x` like `cast(x, mode, ...)` and return the format's one-byte codes (uint8 tensor of x's shape):
-    E5M2 / E4M3 / E3M4 bit layouts of the reference's format table (README.md:17-27)."""
+    E5M2 / E4M3 / E3M4 bit layouts of the reference's format table (README.md:17-27).  `expect_normals`: performance
+    hint for E4M3_RNE that scaled values below 2^-6 are rare (amax-derived scales); never changes a code."""
     _check_tensor(x)
     fmt, rnd, flags = L.parse_mode(mode)
+    if expect_normals:
+        flags |= L.FLAG_EXPECT_NORMALS
     n = x.numel() if n is None else int(n)
     if n > x.numel():
         raise ValueError("fpemu: size larger than the tensor")
@@ -382,11 +385,13 @@ class MultiTensorPlan(object):
             raise ValueError("fpemu: d_scales must be a float32 CUDA vector with one entry per tensor")
         return d_scales.data_ptr()
 
-    def encode(self, mode, d_scales=None, seed=None):
+    def encode(self, mode, d_scales=None, seed=None, expect_normals=False):
         """Round every tensor like `cast` and write one-byte codes into the plan's uint8 outputs, one launch."""
         if not self.packed:
             raise ValueError("fpemu: this plan's outputs are not uint8 code buffers")
         fmt, rnd, flags = L.parse_mode(mode)
+        if expect_normals:
+            flags |= L.FLAG_EXPECT_NORMALS
         if rnd == L.RND_STOCHASTIC and seed is None:
             seed = next_seed()
         with _on_device(self.d_table):
@@ -403,7 +408,7 @@ class MultiTensorPlan(object):
         if reduce_fn is not None:
             reduce_fn(vec)
         scales = scale_from_amax(vec, FLT_MAX[fmt] if flt_max is None else flt_max)
-        return self.encode(mode, d_scales=scales, seed=seed), scales
+        return self.encode(mode, d_scales=scales, seed=seed, expect_normals=True), scales   # scaled to the maximum
 
     def cast(self, mode, d_scales=None, seed=None, unscale_fp32=False):
         """Cast every tensor in one launch; tensor t uses d_scales[t] (None: scale 1) and seed + t."""

@@ -62,8 +62,14 @@ enum {
                                   (cpp/fpemu_impl.cpp:761,1131,1716).  Default (flag clear) rounds the
                                   un-scaled value through fp16 like the reference CUDA op
                                   (fpemu_kernels.cu:461,539,652,982).                                 */
-  FPEMU_FLAG_NO_SCALE_CLAMP = 4 /* fpemu_cast_rowwise only: skip the `6.55e4 if scale > 3.275e4` clamp,
+  FPEMU_FLAG_NO_SCALE_CLAMP = 4, /* fpemu_cast_rowwise only: skip the `6.55e4 if scale > 3.275e4` clamp,
                                   as the fine-grained branch of quantize_tensor does (qutils.py:328-330)  */
+  FPEMU_FLAG_EXPECT_NORMALS = 8 /* fpemu_encode / fpemu_encode_multi, E4M3 + RNE only: a performance hint that
+                                  values below the format's smallest normal (after scaling) are rare, as they are
+                                  when the scale was derived from the tensor's maximum.  Enables the hardware
+                                  fp16 -> e4m3 conversion for vectors made of normals, zeros and overflows (where
+                                  it is bit-identical to the reference's rounding); other vectors are redone
+                                  exactly.  Never changes a result; costs throughput when the hint is wrong.   */
 };
 
 /* Element types of the in/out buffers (both buffers always share one type). */

@@ -42,7 +42,7 @@ class OracleKernels(object):
 
 
     @staticmethod
-    def encode(x, mode, out=None, scale=1.0, d_scale=None, seed=0, elem_offset=0):
+    def encode(x, mode, out=None, scale=1.0, d_scale=None, seed=0, elem_offset=0, expect_normals=False):
         from oracle import fpemu_oracle as O
         s = float(d_scale[0]) if d_scale is not None else scale
         c = torch.from_numpy(O.encode(x.numpy(), mode, scale=s, seed=seed, elem_offset=elem_offset)).reshape(x.shape)

@@ -193,3 +193,19 @@ def test_multi_tensor_amax_scaled_codes_decode_to_the_amax_scaled_cast(F):
         big = (x.abs() * scales[t]) >= 2.0 ** -5
         assert torch.equal(back[big].view(torch.int32), want[t][big].view(torch.int32))
         assert float(big.float().mean()) > 0.99
+
+
+@pytest.mark.parametrize("dt", ["f32", "f16", "bf16"])
+def test_expect_normals_hint_never_changes_a_code(F, dt):
+    """FPEMU_FLAG_EXPECT_NORMALS switches E4M3_RNE to the hardware fp16 -> e4m3 conversion for vectors without
+    sub-normal-range lanes or NaN: every fp16 pattern, wide data (hint badly wrong) and amax-scaled data (hint right)."""
+    for x, scale in ((fp16_patterns(), 1.0), (wide(1 << 17, 51), 1.0), (wide(1 << 16, 52), 3.7)):
+        xn, xt = as_dtype(x, dt)
+        got = F.encode(xt, "E4M3_RNE", scale=scale, expect_normals=True)
+        codes_equal(got, O.encode(xn, "E4M3_RNE", scale=scale), "hint on, %s scale %g" % (dt, scale))
+    g = torch.Generator(device="cuda").manual_seed(2)
+    x = (torch.randn((1 << 20) + 5, device="cuda", generator=g) * 0.02).to(TORCH_DT[dt])
+    s = F.scale_from_amax(F.amax(x), 448.0)
+    assert torch.equal(F.encode(x, "E4M3_RNE", d_scale=s, expect_normals=True), F.encode(x, "E4M3_RNE", d_scale=s))
+    for mode in ("E4M3_STOCHASTIC", "E5M2_RNE", "E3M4_RNE"):                          # ignored for other modes
+        assert torch.equal(F.encode(x, mode, seed=3, expect_normals=True), F.encode(x, mode, seed=3))
