@@ -1,9 +1,9 @@
 """fpemu_b200 — host side of the B200-native fpemu cast (thin ctypes layer over libfpemu_b200.so)."""
 from . import _lib
 from ._lib import FpemuError, parse_mode
-from .ops import (FLT_MAX, HostCaster, MultiTensorPlan, amax, cast, cast_amax_scaled, cast_amax_scaled_noalloc, cast_blocked, cast_rowwise, decode, encode,
+from .ops import (FLT_MAX, HostCaster, MultiTensorPlan, amax, cast, cast_amax_scaled, cast_amax_scaled_noalloc, cast_blocked, cast_rowwise, decode, decode_rowwise, encode, encode_rowwise,
                   manual_seed, next_seed, scale_from_amax)
 
 __all__ = ["FpemuError", "parse_mode", "FLT_MAX", "HostCaster", "MultiTensorPlan", "amax", "cast", "cast_amax_scaled", "cast_amax_scaled_noalloc",
            "cast_blocked",
-           "cast_rowwise", "decode", "encode", "manual_seed", "next_seed", "scale_from_amax", "_lib"]
+           "cast_rowwise", "decode", "decode_rowwise", "encode", "encode_rowwise", "manual_seed", "next_seed", "scale_from_amax", "_lib"]

@@ -328,6 +328,61 @@ def cast_rowwise(x2d, mode, out=None, flt_max=None, clamp=True, seed=None, elem_
     return (out, scales) if return_scales else out
 
 
+def encode_rowwise(x2d, mode, codes=None, scales=None, flt_max=None, clamp=True, seed=None, elem_offset=0, rows=None,
+                   cols=None):
+    """Per-channel wire form: (codes uint8 of x2d's shape, scales float32[rows]) such that
+    `decode_rowwise(codes, scales, ...)` reproduces `cast_rowwise(x2d, mode)`; one launch, each row read once."""
+    _check_tensor(x2d)
+    fmt, rnd, flags = L.parse_mode(mode)
+    if not clamp:
+        flags |= L.FLAG_NO_SCALE_CLAMP
+    if flt_max is None:
+        flt_max = FLT_MAX[fmt]
+    if rows is None:
+        rows = x2d.shape[0] if x2d.dim() > 0 else 1
+        cols = x2d.numel() // max(rows, 1)
+    if codes is None:
+        codes = torch.empty(x2d.shape, dtype=torch.uint8, device=x2d.device)
+    elif not (codes.is_cuda and codes.dtype == torch.uint8 and codes.is_contiguous() and codes.numel() >= rows * cols):
+        raise ValueError("fpemu: codes must be a contiguous uint8 CUDA tensor of rows * cols elements")
+    if scales is None:
+        scales = torch.empty(rows, dtype=torch.float32, device=x2d.device)
+    elif not (scales.is_cuda and scales.dtype == torch.float32 and scales.is_contiguous() and scales.numel() >= rows):
+        raise ValueError("fpemu: scales must be a contiguous float32 CUDA tensor with one entry per row")
+    if rnd == L.RND_STOCHASTIC and seed is None:
+        seed = next_seed()
+    with _on_device(x2d):
+        st = L.lib().fpemu_encode_rowwise(x2d.data_ptr(), codes.data_ptr(), int(rows), int(cols), _dt(x2d), fmt, rnd, flags,
+                                          float(flt_max), scales.data_ptr(), int(seed or 0), int(elem_offset), _stream(x2d))
+    L.check(st, "fpemu_encode_rowwise(%s)" % mode)
+    return codes, scales
+
+
+def decode_rowwise(codes, scales, mode, dtype=torch.float32, out=None, unscale_fp32=False, rows=None, cols=None):
+    """Codes + per-row scales -> values of `dtype` (what `cast_rowwise` returns)."""
+    if not (codes.is_cuda and codes.dtype == torch.uint8 and codes.is_contiguous()):
+        raise ValueError("fpemu: codes must be a contiguous uint8 CUDA tensor")
+    fmt = {"E5M2": L.FMT_E5M2, "E4M3": L.FMT_E4M3, "E3M4": L.FMT_E3M4}.get(mode)
+    if fmt is None:
+        fmt = L.parse_mode(mode)[0]
+    if rows is None:
+        rows = codes.shape[0] if codes.dim() > 0 else 1
+        cols = codes.numel() // max(rows, 1)
+    if not (scales.is_cuda and scales.dtype == torch.float32 and scales.is_contiguous() and scales.numel() >= rows):
+        raise ValueError("fpemu: scales must be a contiguous float32 CUDA tensor with one entry per row")
+    if out is None:
+        out = torch.empty(codes.shape, dtype=dtype, device=codes.device)
+    else:
+        _check_tensor(out, "out")
+        if out.numel() < rows * cols:
+            raise ValueError("fpemu: out too small")
+    with _on_device(codes):
+        st = L.lib().fpemu_decode_rowwise(codes.data_ptr(), out.data_ptr(), int(rows), int(cols), _dt(out), fmt,
+                                          L.FLAG_UNSCALE_FP32 if unscale_fp32 else 0, scales.data_ptr(), _stream(codes))
+    L.check(st, "fpemu_decode_rowwise(%s)" % mode)
+    return out
+
+
 class MultiTensorPlan(object):
     """A fixed list of CUDA tensors (same dtype, same device) that is reduced / cast with ONE launch each.
 

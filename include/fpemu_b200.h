@@ -180,6 +180,19 @@ FPEMU_API int fpemu_encode(const void* in, void* codes, int64_t n, int dtype, in
 FPEMU_API int fpemu_decode(const void* codes, void* out, int64_t n, int dtype, int format, int flags, float scale,
                  const float* d_scale, void* stream);
 
+/* Per-channel wire form: the rounding of fpemu_cast_rowwise (each row scaled by clamp(flt_max / max|row|), mpemu/qutils.py:
+ * 289-311; FPEMU_FLAG_NO_SCALE_CLAMP for the fine-grained branch :313-337) stored as one code per element plus one float
+ * per row in d_row_scale (required), and the way back.  Rows up to 12 288 float32 / 24 576 16-bit elements are encoded in
+ * a single pass from registers (`in` 32-byte aligned, `codes` 8- / 16-byte aligned, cols a multiple of 8 / 16, and of 16
+ * with elem_offset % 16 == 0 for stochastic rounding); anything else runs one warp per row in two passes.
+ * fpemu_decode_rowwise(fpemu_encode_rowwise(x)) equals fpemu_cast_rowwise(x) wherever the rounded value is a member of
+ * the format (fpemu_encode above). */
+FPEMU_API int fpemu_encode_rowwise(const void* in, void* codes, int64_t rows, int64_t cols, int dtype, int format,
+                         int rounding, int flags, float flt_max, float* d_row_scale, uint64_t seed,
+                         uint64_t elem_offset, void* stream);
+FPEMU_API int fpemu_decode_rowwise(const void* codes, void* out, int64_t rows, int64_t cols, int dtype, int format,
+                         int flags, const float* d_row_scale, void* stream);
+
 /* Host-buffer convenience used by the end-to-end measurement: casts n elements that live in HOST
  * memory (pinned for full speed) into a HOST output, staging through two caller-provided device
  * buffers of chunk_elems elements each (d_stage[0], d_stage[1]) so the H2D copy, the kernel and the

@@ -197,6 +197,25 @@ def cast_rowwise(x2d, mode, flt_max, unscale_fp32=False):
     return out, scales
 
 
+def encode_rowwise(x2d, mode, flt_max, seed=0, elem_offset=0):
+    """Per-channel codes + scales: the same loop, `encode` instead of `cast` (row r starts at element r * cols)."""
+    x2d = np.ascontiguousarray(x2d)
+    codes = np.empty(x2d.shape, dtype=np.uint8)
+    scales = np.empty(x2d.shape[0], dtype=np.float32)
+    for r in range(x2d.shape[0]):
+        s = scale_from_amax(amax(x2d[r]), flt_max)
+        scales[r] = s
+        codes[r] = encode(x2d[r], mode, scale=s, seed=seed, elem_offset=elem_offset + r * x2d.shape[1])
+    return codes, scales
+
+
+def decode_rowwise(codes, scales, fmt_name, dtype=np.float32, unscale_fp32=False):
+    out = np.empty(codes.shape, dtype=dtype)
+    for r in range(codes.shape[0]):
+        out[r] = decode(codes[r], fmt_name, dtype=dtype, scale=float(scales[r]), unscale_fp32=unscale_fp32)
+    return out
+
+
 def philox(seed, ctr):
     out = (ctypes.c_uint32 * 4)()
     lib().fpemu_oracle_philox4x32_10(seed, ctr, out)

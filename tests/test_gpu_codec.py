@@ -209,3 +209,45 @@ def test_expect_normals_hint_never_changes_a_code(F, dt):
     assert torch.equal(F.encode(x, "E4M3_RNE", d_scale=s, expect_normals=True), F.encode(x, "E4M3_RNE", d_scale=s))
     for mode in ("E4M3_STOCHASTIC", "E5M2_RNE", "E3M4_RNE"):                          # ignored for other modes
         assert torch.equal(F.encode(x, mode, seed=3, expect_normals=True), F.encode(x, mode, seed=3))
+
+
+@pytest.mark.parametrize("mode", ["E4M3_RNE", "E5M2_STOCHASTIC", "E3M4_RTZ", "E4M3_STOCHASTIC", "E5M2_RNAZ"])
+@pytest.mark.parametrize("dt", ["f32", "f16", "bf16"])
+@pytest.mark.parametrize("shape", [(7, 64), (64, 576), (33, 4096), (5, 12288), (3, 12288 + 32), (9, 100)])
+def test_rowwise_codes_and_scales_vs_oracle(F, mode, dt, shape):
+    """Per-channel wire form: codes and per-row scales against the oracle's per-row loop; rows in registers (warp- and
+    CTA-sized), rows too long for registers, and a column count that is not a vector multiple (one warp per row)."""
+    fmt = mode.split("_")[0]
+    flt_max = {"E5M2": 57344.0, "E4M3": 448.0, "E3M4": 30.0}[fmt]
+    rng = np.random.default_rng(shape[0] * 1000 + shape[1])
+    x = (rng.standard_normal(shape) * np.exp2(rng.integers(-6, 3, (shape[0], 1)))).astype(np.float32)
+    xn, xt = as_dtype(x.reshape(-1), dt)
+    xn, xt = xn.reshape(shape), xt.reshape(shape)
+    codes, scales = F.encode_rowwise(xt, mode, seed=21)
+    want_codes, want_scales = O.encode_rowwise(xn, mode, flt_max, seed=21)
+    assert (scales.cpu().numpy() == want_scales).all()
+    codes_equal(codes, want_codes, "%s %s %s" % (mode, dt, shape))
+    np_dt = {"f32": np.float32, "f16": np.float16, "bf16": np.uint16}[dt]
+    for unscale_fp32 in (False, True):
+        back = F.decode_rowwise(codes, scales, fmt, dtype=TORCH_DT[dt], unscale_fp32=unscale_fp32)
+        got = host(back)
+        want = O.decode_rowwise(want_codes, want_scales, fmt, dtype=np_dt, unscale_fp32=unscale_fp32)
+        if dt == "bf16":
+            got, want = (got.astype(np.uint32) << 16).view(np.float32), (want.astype(np.uint32) << 16).view(np.float32)
+        assert_same(got.reshape(-1), want.reshape(-1), "decode %s %s %s" % (mode, dt, shape))
+
+
+def test_rowwise_round_trip_reproduces_cast_rowwise(F):
+    g = torch.Generator(device="cuda").manual_seed(4)
+    for shape in ((4096, 4096), (512, 11008), (1000, 576)):
+        x = torch.randn(shape, device="cuda", generator=g) * 0.02
+        q, s0 = F.cast_rowwise(x, "E4M3_RNE", return_scales=True)
+        codes, s1 = F.encode_rowwise(x, "E4M3_RNE")
+        assert torch.equal(s0, s1)
+        back = F.decode_rowwise(codes, s1, "E4M3")
+        big = (x.abs() * s1[:, None]) >= 2.0 ** -5
+        assert torch.equal(back[big].view(torch.int32), q[big].view(torch.int32))
+        assert float(big.float().mean()) > 0.99
+        q5, s5 = F.cast_rowwise(x, "E5M2_RNE", return_scales=True)
+        c5, t5 = F.encode_rowwise(x, "E5M2_RNE")
+        assert torch.equal(F.decode_rowwise(c5, t5, "E5M2").view(torch.int32), q5.view(torch.int32))

@@ -68,6 +68,27 @@ def main():
             print(rows[-1], flush=True)
         del x, y, c
         torch.cuda.empty_cache()
+    # per-channel wire form on weight-matrix shapes
+    for dname, dtype in (("fp32", torch.float32), ("bf16", torch.bfloat16)):
+        esz = 4 if dtype == torch.float32 else 2
+        for shape in ((32000, 4096), (11008, 4096), (4096, 11008), (4096, 4096)):
+            x = (torch.randn(shape, device="cuda") * 0.02).to(dtype)
+            c = torch.empty(shape, dtype=torch.uint8, device="cuda")
+            sc = torch.empty(shape[0], dtype=torch.float32, device="cuda")
+            y = torch.empty_like(x)
+            nn = x.numel()
+            ms = timed(lambda: F.encode_rowwise(x, "E4M3_RNE", codes=c, scales=sc))
+            rows.append({"op": "encode_rowwise", "mode": "E4M3_RNE", "dtype": dname, "shape": list(shape), "ms": ms,
+                         "GB/s": nn * (esz + 1) / ms / 1e6, "Gelem/s": nn / ms / 1e6})
+            print(rows[-1], flush=True)
+            ms = timed(lambda: F.decode_rowwise(c, sc, "E4M3", out=y))
+            rows.append({"op": "decode_rowwise", "mode": "E4M3", "dtype": dname, "shape": list(shape), "ms": ms,
+                         "GB/s": nn * (esz + 1) / ms / 1e6, "Gelem/s": nn / ms / 1e6})
+            print(rows[-1], flush=True)
+            ms = timed(lambda: F.cast_rowwise(x, "E4M3_RNE", out=y))
+            rows.append({"op": "cast_rowwise", "mode": "E4M3_RNE", "dtype": dname, "shape": list(shape), "ms": ms,
+                         "GB/s": nn * 2 * esz / ms / 1e6, "Gelem/s": nn / ms / 1e6})
+            print(rows[-1], flush=True)
     os.makedirs(os.path.dirname(args.out), exist_ok=True)
     json.dump({"gpu": torch.cuda.get_device_name(0), "log2n": args.log2n, "rows": rows}, open(args.out, "w"), indent=0)
 
