@@ -8,25 +8,21 @@
 //
 // Encode: same shape as the register-resident row kernel (fpemu_group.cu) — a warp or a CTA loads its row once,
 // reduces |x|, derives the scale and emits codes from the registers: read 1 element + write 1 byte, single pass.
-// Rows that do not fit (more than 12 288 fp32 / 24 576 16-bit elements), unaligned buffers or columns, and modes
+// Rows that do not fit (more than 16 384 fp32 / 32 768 16-bit elements), unaligned buffers or columns, and modes
 // without a packed kernel use one warp per row, two passes, element-wise.
 // Decode: one pass over the codes; each 32-byte output vector looks up its row's scale.
 #include "fpemu_codec_core.cuh"
-#include "fpemu_reduce.cuh"
+#include "fpemu_group_core.cuh"
 
 namespace fpemu {
 
-constexpr int kRowsWarpR = 4;        // 32 * 4 = 128 vectors per row
-constexpr int kRowsCtaSmallR = 2;    // 256 * 2 = 512 vectors per row
-constexpr int kRowsCtaR = 6;         // 256 * 6 = 1536 vectors per row
-
-template <int FMT, int RND, int DT, int G, int R>
-__global__ void __launch_bounds__(256) encode_rows_kernel(const CastArgs a, const int64_t rows, const int vpr,
+template <int FMT, int RND, int DT, int R>
+__global__ void __launch_bounds__(256) encode_rows_kernel(const CastArgs a, const int64_t rows, const int vpr, const int lg,
                                                          const bool clamp, const float flt_max, float* d_row_scale) {
   constexpr int VE = DtInfo<DT>::kVecElems;
-  constexpr int kRowsPerCta = 256 / G;
-  const int tg = threadIdx.x % G;
-  const int64_t row = (int64_t)blockIdx.x * kRowsPerCta + threadIdx.x / G;
+  const int G = 1 << lg;
+  const int tg = threadIdx.x & (G - 1);
+  const int64_t row = (int64_t)blockIdx.x * (256 >> lg) + (threadIdx.x >> lg);
   const bool live = row < rows;
   const int64_t v0 = row * vpr;
   const char* in = static_cast<const char*>(a.in);
@@ -44,16 +40,7 @@ __global__ void __launch_bounds__(256) encode_rows_kernel(const CastArgs a, cons
   }
 #pragma unroll
   for (int j = 0; j < R; ++j) m = fmaxf(m, vec_absmax<DT>(v[j]));
-  uint32_t bits = warp_max_u32(__float_as_uint(m));
-  if (G > 32) {
-    __shared__ uint32_t warp_bits[8];
-    if ((threadIdx.x & 31) == 0) warp_bits[threadIdx.x >> 5] = bits;
-    __syncthreads();
-    bits = warp_bits[0];
-#pragma unroll
-    for (int w = 1; w < 8; ++w) bits = max(bits, warp_bits[w]);
-  }
-  const float s_host = scale_from_amax(__uint_as_float(bits), flt_max, clamp);
+  const float s_host = scale_from_amax(group_absmax(m, lg), flt_max, clamp);
   if (live && tg == 0) d_row_scale[row] = s_host;
   ScaleCtx sc;
   sc.scale = effective_scale(s_host, DT);
@@ -149,14 +136,14 @@ __global__ void __launch_bounds__(256) decode_rows_generic_kernel(const CastArgs
   }
 }
 
-typedef void (*EncRowsKernel)(const CastArgs, const int64_t, const int, const bool, const float, float*);
+typedef void (*EncRowsKernel)(const CastArgs, const int64_t, const int, const int, const bool, const float, float*);
 typedef void (*DecRowsKernel)(const CastArgs, const int64_t, const float*);
 
 template <int FMT, int RND, int DT>
-static EncRowsKernel er_shape(int shape) {
-  if (shape == 0) return encode_rows_kernel<FMT, RND, DT, 32, kRowsWarpR>;
-  if (shape == 1) return encode_rows_kernel<FMT, RND, DT, 256, kRowsCtaSmallR>;
-  return encode_rows_kernel<FMT, RND, DT, 256, kRowsCtaR>;
+static EncRowsKernel er_shape(int r) {
+  if (r == 4) return encode_rows_kernel<FMT, RND, DT, 4>;
+  if (r == 6) return encode_rows_kernel<FMT, RND, DT, 6>;
+  return encode_rows_kernel<FMT, RND, DT, 8>;
 }
 template <int FMT, int RND>
 static EncRowsKernel er_dt(int dt, int shape) {
@@ -225,18 +212,18 @@ extern "C" int fpemu_encode_rowwise(const void* in, void* codes, int64_t rows, i
   const bool aligned = ((uintptr_t)in % 32u) == 0 && ((uintptr_t)codes % code_align) == 0 && cols % ve == 0;
   const bool rng_ok = (rounding != FPEMU_RND_STOCHASTIC) || ((elem_offset & 15u) == 0 && cols % 16 == 0);
   const int64_t vpr = cols / ve;
-  if (aligned && rng_ok && !(flags & FPEMU_FLAG_DAZ) && vpr >= 1 && vpr <= 256 * kRowsCtaR) {
-    const int shape = vpr <= 32 * kRowsWarpR ? 0 : (vpr <= 256 * kRowsCtaSmallR ? 1 : 2);
+  int lg = 0, r = 0;
+  if (aligned && rng_ok && !(flags & FPEMU_FLAG_DAZ) && group_shape(vpr, &lg, &r)) {
     EncRowsKernel k = nullptr;
     switch (format) {
-      case FPEMU_FMT_E5M2: k = er_rnd<FPEMU_FMT_E5M2>(rounding, dtype, shape); break;
-      case FPEMU_FMT_E4M3: k = er_rnd<FPEMU_FMT_E4M3>(rounding, dtype, shape); break;
-      default:             k = er_rnd<FPEMU_FMT_E3M4>(rounding, dtype, shape); break;
+      case FPEMU_FMT_E5M2: k = er_rnd<FPEMU_FMT_E5M2>(rounding, dtype, r); break;
+      case FPEMU_FMT_E4M3: k = er_rnd<FPEMU_FMT_E4M3>(rounding, dtype, r); break;
+      default:             k = er_rnd<FPEMU_FMT_E3M4>(rounding, dtype, r); break;
     }
-    const int64_t per_cta = shape ? 1 : 8;
+    const int64_t per_cta = 256 >> lg;
     const int64_t grid = (rows + per_cta - 1) / per_cta;
     if (k != nullptr && grid <= 0x7FFFFFFFLL) {
-      k<<<(unsigned)grid, 256, 0, stream>>>(a, rows, (int)vpr, clamp, flt_max, d_row_scale);
+      k<<<(unsigned)grid, 256, 0, stream>>>(a, rows, (int)vpr, lg, clamp, flt_max, d_row_scale);
       return (int)cudaGetLastError();
     }
   }

@@ -182,7 +182,7 @@ FPEMU_API int fpemu_decode(const void* codes, void* out, int64_t n, int dtype, i
 
 /* Per-channel wire form: the rounding of fpemu_cast_rowwise (each row scaled by clamp(flt_max / max|row|), mpemu/qutils.py:
  * 289-311; FPEMU_FLAG_NO_SCALE_CLAMP for the fine-grained branch :313-337) stored as one code per element plus one float
- * per row in d_row_scale (required), and the way back.  Rows up to 12 288 float32 / 24 576 16-bit elements are encoded in
+ * per row in d_row_scale (required), and the way back.  Rows up to 16 384 float32 / 32 768 16-bit elements are encoded in
  * a single pass from registers (`in` 32-byte aligned, `codes` 8- / 16-byte aligned, cols a multiple of 8 / 16, and of 16
  * with elem_offset % 16 == 0 for stochastic rounding); anything else runs one warp per row in two passes.
  * fpemu_decode_rowwise(fpemu_encode_rowwise(x)) equals fpemu_cast_rowwise(x) wherever the rounded value is a member of
