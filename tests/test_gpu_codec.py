@@ -251,3 +251,32 @@ def test_rowwise_round_trip_reproduces_cast_rowwise(F):
         q5, s5 = F.cast_rowwise(x, "E5M2_RNE", return_scales=True)
         c5, t5 = F.encode_rowwise(x, "E5M2_RNE")
         assert torch.equal(F.decode_rowwise(c5, t5, "E5M2").view(torch.int32), q5.view(torch.int32))
+
+
+def test_codec_calls_inside_a_cuda_graph(F):
+    x = torch.randn(1 << 18, device="cuda")
+    x2 = torch.randn(256, 1024, device="cuda")
+    codes = torch.empty(x.numel(), dtype=torch.uint8, device="cuda")
+    back = torch.empty_like(x)
+    rc = torch.empty(x2.shape, dtype=torch.uint8, device="cuda")
+    rs = torch.empty(256, dtype=torch.float32, device="cuda")
+    rb = torch.empty_like(x2)
+    s = torch.cuda.Stream()
+    with torch.cuda.stream(s):
+        def work():
+            F.encode(x, "E4M3_STOCHASTIC", out=codes, seed=3)
+            F.decode(codes, "E4M3", out=back)
+            F.encode_rowwise(x2, "E5M2_RNE", codes=rc, scales=rs)
+            F.decode_rowwise(rc, rs, "E5M2", out=rb)
+        work()
+        s.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, stream=s):
+            work()
+    x.mul_(1.7)
+    x2.add_(0.3)
+    graph.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(codes, F.encode(x, "E4M3_STOCHASTIC", seed=3))
+    assert torch.equal(back, F.decode(codes, "E4M3"))
+    assert torch.equal(rb.view(torch.int32), F.cast_rowwise(x2, "E5M2_RNE").view(torch.int32))
