@@ -3,7 +3,7 @@
 
 #include <mutex>
 
-#include "fpemu_common.cuh"
+#include "fpemu_cast_core.cuh"
 
 namespace fpemu {
 
@@ -24,7 +24,38 @@ const DeviceInfo& device_info() {
   return info[dev];
 }
 
+namespace {
+const unsigned long long* g_seed_source[64];
+std::mutex g_seed_mu;
+__global__ void advance_seed_kernel(unsigned long long* p) { *p += 0x9E3779B97F4A7C15ull; }
+}  // namespace
+
+const unsigned long long* seed_source() {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64) return nullptr;
+  std::lock_guard<std::mutex> lock(g_seed_mu);
+  return g_seed_source[dev];
+}
+
 }  // namespace fpemu
+
+extern "C" int fpemu_set_seed_source(const uint64_t* d_seed) {
+  int dev = 0;
+  cudaError_t err = cudaGetDevice(&dev);
+  if (err != cudaSuccess) return (int)err;
+  if (dev < 0 || dev >= 64) return FPEMU_ERR_ARG;
+  std::lock_guard<std::mutex> lock(fpemu::g_seed_mu);
+  fpemu::g_seed_source[dev] = reinterpret_cast<const unsigned long long*>(d_seed);
+  return FPEMU_OK;
+}
+
+extern "C" int fpemu_advance_seed_source(void* stream) {
+  const unsigned long long* p = fpemu::seed_source();
+  if (p == nullptr) return FPEMU_ERR_ARG;
+  fpemu::advance_seed_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(const_cast<unsigned long long*>(p));
+  return (int)cudaGetLastError();
+}
 
 extern "C" int fpemu_version(void) { return 100; }  // 0.1.0
 

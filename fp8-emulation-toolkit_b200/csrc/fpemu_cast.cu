@@ -12,7 +12,8 @@
 namespace fpemu {
 
 template <int FMT, int RND, bool DAZ, int DT, bool SCALED>
-__global__ void __launch_bounds__(kThreads) cast_vec_kernel(const CastArgs a) {
+__global__ void __launch_bounds__(kThreads) cast_vec_kernel(const CastArgs a_) {
+  const CastArgs a = with_device_seed(a_);
   constexpr int VE = DtInfo<DT>::kVecElems;
   const ScaleCtx sc = make_scale_ctx<DT, SCALED>(a);
   const int64_t nvec = a.n / VE;
@@ -63,7 +64,8 @@ __global__ void __launch_bounds__(kThreads) cast_vec_kernel(const CastArgs a) {
 }
 
 // Every format x rounding mode, any alignment, per-element random draws.  Correctness path, not the fast one.
-__global__ void __launch_bounds__(256) cast_generic_kernel(const CastArgs a, const int dt) {
+__global__ void __launch_bounds__(256) cast_generic_kernel(const CastArgs a_, const int dt) {
+  const CastArgs a = with_device_seed(a_);
   const bool scaled = (a.d_scale != nullptr) || (a.d_amax != nullptr) || (a.scale != 1.0f);
   float s = 1.0f, rs = 1.0f;
   if (scaled) {
@@ -97,6 +99,7 @@ __global__ void __launch_bounds__(kThreads) cast_vec_generic_kernel(const CastAr
   CastArgs a = a_;
   if (CFMT >= 0) a.fmt = CFMT;
   if (CRND >= 0) a.rnd = CRND;
+  a = with_device_seed(a);
   const bool scaled = (a.d_scale != nullptr) || (a.d_amax != nullptr) || (a.scale != 1.0f);
   float s = 1.0f, rs = 1.0f;
   if (scaled) {
@@ -292,7 +295,7 @@ extern "C" int fpemu_cast(const void* in, void* out, int64_t n, int dtype, int f
   a.seed_lo = (uint32_t)seed; a.seed_hi = (uint32_t)(seed >> 32);
   a.elem_offset = elem_offset;
   a.fmt = format; a.rnd = rounding; a.flags = flags;
-  a.d_amax = nullptr; a.flt_max = 0.0f; a.d_scale_out = nullptr;
+  a.d_amax = nullptr; a.flt_max = 0.0f; a.d_scale_out = nullptr; a.d_seed = fpemu::seed_source();
   if (format == FPEMU_FMT_BF16 || format == FPEMU_FMT_FP16) { a.scale = 1.0f; a.d_scale = nullptr; }  // no scale in these kernels
   return fpemu::launch_cast(a, dtype, static_cast<cudaStream_t>(stream));
 }

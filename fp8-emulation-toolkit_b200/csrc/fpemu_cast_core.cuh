@@ -19,7 +19,24 @@ struct CastArgs {
   const float* d_amax;
   float flt_max;
   float* d_scale_out;
+  // optional: a device-resident 64-bit word added to the seed when the kernel starts (fpemu_set_seed_source), so that
+  // a captured CUDA graph draws fresh random bits on every replay
+  const unsigned long long* d_seed;
 };
+
+// The seed a stochastic kernel uses: the host-side seed of the call plus the device-side word, if one is installed.
+__device__ __forceinline__ CastArgs with_device_seed(const CastArgs& in) {
+  CastArgs a = in;
+  if (a.rnd == FPEMU_RND_STOCHASTIC && a.d_seed != nullptr) {
+    const unsigned long long s = (((unsigned long long)a.seed_hi << 32) | a.seed_lo) + __ldg(a.d_seed);
+    a.seed_lo = (uint32_t)s;
+    a.seed_hi = (uint32_t)(s >> 32);
+  }
+  return a;
+}
+
+// Host side: the device word installed for the current device (nullptr when none), fpemu_api.cu.
+const unsigned long long* seed_source();
 
 constexpr int kThreads = 256;
 // 32-byte vectors in flight per thread (tuned on B200, profiles/tune_r1.txt): fp32 is HBM-bound with 2;

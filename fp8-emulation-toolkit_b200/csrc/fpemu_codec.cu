@@ -14,7 +14,8 @@
 namespace fpemu {
 
 template <int FMT, int RND, bool DAZ, int DT, bool SCALED>
-__global__ void __launch_bounds__(kThreads) encode_vec_kernel(const CastArgs a) {
+__global__ void __launch_bounds__(kThreads) encode_vec_kernel(const CastArgs a_) {
+  const CastArgs a = with_device_seed(a_);
   const ScaleCtx sc = make_scale_ctx<DT, SCALED>(a);
   encode_cta<FMT, RND, DAZ, DT, SCALED, CodecUnroll<DT>::value>(a, sc, (int64_t)blockIdx.x, blockIdx.x == gridDim.x - 1);
 }
@@ -73,7 +74,8 @@ __global__ void __launch_bounds__(kThreads) decode_vec_kernel(const CastArgs a) 
 }
 
 // Any alignment, any rounding mode of the three formats: one element per thread-iteration.
-__global__ void __launch_bounds__(256) encode_generic_kernel(const CastArgs a, const int dt) {
+__global__ void __launch_bounds__(256) encode_generic_kernel(const CastArgs a_, const int dt) {
+  const CastArgs a = with_device_seed(a_);
   const bool scaled = (a.d_scale != nullptr) || (a.scale != 1.0f);
   float s = 1.0f;
   if (scaled) s = effective_scale(a.d_scale ? __ldg(a.d_scale) : a.scale, dt);
@@ -180,7 +182,7 @@ static CastArgs codec_args(const void* in, void* out, int64_t n, int format, int
   a.seed_lo = (uint32_t)seed; a.seed_hi = (uint32_t)(seed >> 32);
   a.elem_offset = elem_offset;
   a.fmt = format; a.rnd = rounding; a.flags = flags;
-  a.d_amax = nullptr; a.flt_max = 0.0f; a.d_scale_out = nullptr;
+  a.d_amax = nullptr; a.flt_max = 0.0f; a.d_scale_out = nullptr; a.d_seed = seed_source();
   return a;
 }
 

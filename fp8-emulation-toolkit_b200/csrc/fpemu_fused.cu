@@ -27,7 +27,8 @@ int validate_cast(int64_t n, int dtype, int format, int rounding, float scale, c
 constexpr int kFusedR = 4;                 // 32-byte vectors a thread keeps in registers across the barrier
 
 template <int FMT, int RND, int DT>
-__global__ void __launch_bounds__(kThreads) fused_amax_cast_kernel(const CastArgs a, float* d_work) {
+__global__ void __launch_bounds__(kThreads) fused_amax_cast_kernel(const CastArgs a_, float* d_work) {
+  const CastArgs a = with_device_seed(a_);
   constexpr int VE = DtInfo<DT>::kVecElems;
   constexpr int R = kFusedR;
   cg::grid_group grid = cg::this_grid();
@@ -194,7 +195,7 @@ extern "C" int fpemu_cast_amax_scaled_fused(const void* in, void* out, int64_t n
       a.seed_lo = (uint32_t)seed; a.seed_hi = (uint32_t)(seed >> 32);
       a.elem_offset = elem_offset;
       a.fmt = format; a.rnd = rounding; a.flags = flags;
-      a.d_amax = nullptr; a.flt_max = flt_max; a.d_scale_out = nullptr;
+      a.d_amax = nullptr; a.flt_max = flt_max; a.d_scale_out = nullptr; a.d_seed = seed_source();
       void* args[] = {(void*)&a, (void*)&d_work};
       cudaError_t err = cudaLaunchCooperativeKernel((const void*)k, dim3((unsigned)ctas), dim3(kThreads), args, 0,
                                                     static_cast<cudaStream_t>(stream_));

@@ -11,8 +11,9 @@ namespace fpemu {
 enum { kRuleRowClamp = 0, kRuleRowNoClamp = 1, kRuleBlockPow2 = 2 };
 
 template <int FMT, int RND, int DT, int R>
-__global__ void __launch_bounds__(256) group_reg_kernel(const CastArgs a, const int64_t groups, const int vpg, const int lg,
+__global__ void __launch_bounds__(256) group_reg_kernel(const CastArgs a_, const int64_t groups, const int vpg, const int lg,
                                                        const int rule, const float flt_max, float* d_scale_out) {
+  const CastArgs a = with_device_seed(a_);
   constexpr int VE = DtInfo<DT>::kVecElems;
   const int G = 1 << lg;
   const int tg = threadIdx.x & (G - 1);

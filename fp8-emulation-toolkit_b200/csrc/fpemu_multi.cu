@@ -64,6 +64,7 @@ __global__ void __launch_bounds__(kThreads) cast_multi_kernel(const void* table,
   a.in = e.in; a.out = e.out; a.n = e.n; a.elem_offset = e.elem_offset;
   a.seed_lo = proto.seed_lo + (uint32_t)t;                       // tensor t uses seed + t
   a.seed_hi = proto.seed_hi + (a.seed_lo < proto.seed_lo ? 1u : 0u);
+  a = with_device_seed(a);
   ScaleCtx sc;
   sc.scale = 1.0f; sc.rscale = 1.0f;
   sc.unscale32 = (a.flags & FPEMU_FLAG_UNSCALE_FP32) != 0;
@@ -130,6 +131,7 @@ __global__ void __launch_bounds__(kThreads) encode_multi_kernel(const void* tabl
   a.in = e.in; a.out = e.out; a.n = e.n; a.elem_offset = e.elem_offset;
   a.seed_lo = proto.seed_lo + (uint32_t)t;                       // tensor t uses seed + t
   a.seed_hi = proto.seed_hi + (a.seed_lo < proto.seed_lo ? 1u : 0u);
+  a = with_device_seed(a);
   ScaleCtx sc;
   sc.scale = 1.0f; sc.rscale = 1.0f; sc.unscale32 = false;
   if (SCALED) {
@@ -298,7 +300,7 @@ extern "C" int fpemu_cast_multi(const void* d_table, const void* h_table, int co
   proto.seed_lo = (uint32_t)seed; proto.seed_hi = (uint32_t)(seed >> 32);
   proto.elem_offset = 0;
   proto.fmt = format; proto.rnd = rounding; proto.flags = flags;
-  proto.d_amax = nullptr; proto.flt_max = 0.0f; proto.d_scale_out = nullptr;
+  proto.d_amax = nullptr; proto.flt_max = 0.0f; proto.d_scale_out = nullptr; proto.d_seed = seed_source();
   k<<<h->total_cast, kThreads, 0, static_cast<cudaStream_t>(stream_)>>>(d_table, count, proto, d_scales);
   return (int)cudaGetLastError();
 }
@@ -326,7 +328,7 @@ extern "C" int fpemu_encode_multi(const void* d_table, const void* h_table, int 
   proto.seed_lo = (uint32_t)seed; proto.seed_hi = (uint32_t)(seed >> 32);
   proto.elem_offset = 0;
   proto.fmt = format; proto.rnd = rounding; proto.flags = flags;
-  proto.d_amax = nullptr; proto.flt_max = 0.0f; proto.d_scale_out = nullptr;
+  proto.d_amax = nullptr; proto.flt_max = 0.0f; proto.d_scale_out = nullptr; proto.d_seed = seed_source();
   k<<<h->total_cast, kThreads, 0, static_cast<cudaStream_t>(stream_)>>>(d_table, count, proto, d_scales);
   return (int)cudaGetLastError();
 }

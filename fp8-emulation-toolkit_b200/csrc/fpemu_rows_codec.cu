@@ -17,8 +17,9 @@
 namespace fpemu {
 
 template <int FMT, int RND, int DT, int R>
-__global__ void __launch_bounds__(256) encode_rows_kernel(const CastArgs a, const int64_t rows, const int vpr, const int lg,
+__global__ void __launch_bounds__(256) encode_rows_kernel(const CastArgs a_, const int64_t rows, const int vpr, const int lg,
                                                          const bool clamp, const float flt_max, float* d_row_scale) {
+  const CastArgs a = with_device_seed(a_);
   constexpr int VE = DtInfo<DT>::kVecElems;
   const int G = 1 << lg;
   const int tg = threadIdx.x & (G - 1);
@@ -59,9 +60,10 @@ __global__ void __launch_bounds__(256) encode_rows_kernel(const CastArgs a, cons
 }
 
 // One warp per row, two passes, any alignment, any rounding mode of the three formats.
-__global__ void __launch_bounds__(256) encode_rows_generic_kernel(const CastArgs a, const int64_t rows, const int64_t cols,
+__global__ void __launch_bounds__(256) encode_rows_generic_kernel(const CastArgs a_, const int64_t rows, const int64_t cols,
                                                                  const int dt, const bool clamp, const float flt_max,
                                                                  float* d_row_scale) {
+  const CastArgs a = with_device_seed(a_);
   const int lane = threadIdx.x & 31;
   const int64_t warp0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
@@ -190,7 +192,7 @@ static CastArgs rows_args(const void* in, void* out, int64_t n, int format, int 
   a.seed_lo = (uint32_t)seed; a.seed_hi = (uint32_t)(seed >> 32);
   a.elem_offset = elem_offset;
   a.fmt = format; a.rnd = rounding; a.flags = flags;
-  a.d_amax = nullptr; a.flt_max = 0.0f; a.d_scale_out = nullptr;
+  a.d_amax = nullptr; a.flt_max = 0.0f; a.d_scale_out = nullptr; a.d_seed = seed_source();
   return a;
 }
 

@@ -67,7 +67,8 @@ __global__ void scale_from_amax_kernel(const float* d_amax, int count, float flt
 // Fast path: a quantization block is `vpb` (power of two, <= 32) consecutive 32-byte vectors, i.e. it lives in
 // `vpb` adjacent lanes of one warp: xor-shuffle butterfly, everything stays in registers (8 B/elem fp32).
 template <int FMT, int RND, int DT>
-__global__ void __launch_bounds__(kThreads) blocked_vec_kernel(const CastArgs a, const int vpb) {
+__global__ void __launch_bounds__(kThreads) blocked_vec_kernel(const CastArgs a_, const int vpb) {
+  const CastArgs a = with_device_seed(a_);
   constexpr int VE = DtInfo<DT>::kVecElems;
   const int64_t nvec = a.n / VE;                            // n % block_size == 0 and block_size % VE == 0
   const char* in = static_cast<const char*>(a.in);
@@ -99,7 +100,8 @@ __global__ void __launch_bounds__(kThreads) blocked_vec_kernel(const CastArgs a,
 
 // General path: one warp per quantization block of any size / alignment / format; two passes over the block
 // (the second one is served by L1/L2).
-__global__ void __launch_bounds__(256) blocked_generic_kernel(const CastArgs a, const int64_t block_size, const int dt) {
+__global__ void __launch_bounds__(256) blocked_generic_kernel(const CastArgs a_, const int64_t block_size, const int dt) {
+  const CastArgs a = with_device_seed(a_);
   const int lane = threadIdx.x & 31;
   const int64_t nblocks = a.n / block_size;
   const int64_t warp0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -153,8 +155,9 @@ static BlockedKernel pick_blocked(int fmt, int rnd, int dt) {
 // One warp per row: pass 1 = |x| max of the row, pass 2 = cast with scale clamp(flt_max / max).  The row is
 // re-read from L1/L2 (rows of Linear/Conv weights are a few KB), so DRAM traffic stays 8 B/elem (fp32).
 template <int FMT, int RND, int DT>
-__global__ void __launch_bounds__(kThreads) rowwise_vec_kernel(const CastArgs a, const int64_t rows, const int64_t cols,
+__global__ void __launch_bounds__(kThreads) rowwise_vec_kernel(const CastArgs a_, const int64_t rows, const int64_t cols,
                                                               const float flt_max, float* d_row_scale, const bool clamp) {
+  const CastArgs a = with_device_seed(a_);
   constexpr int VE = DtInfo<DT>::kVecElems;
   const int lane = threadIdx.x & 31;
   const int64_t warp0 = ((int64_t)blockIdx.x * kThreads + threadIdx.x) >> 5;
@@ -184,9 +187,10 @@ __global__ void __launch_bounds__(kThreads) rowwise_vec_kernel(const CastArgs a,
   }
 }
 
-__global__ void __launch_bounds__(256) rowwise_generic_kernel(const CastArgs a, const int64_t rows, const int64_t cols,
+__global__ void __launch_bounds__(256) rowwise_generic_kernel(const CastArgs a_, const int64_t rows, const int64_t cols,
                                                              const int dt, const float flt_max, float* d_row_scale,
                                                              const bool clamp) {
+  const CastArgs a = with_device_seed(a_);
   const int lane = threadIdx.x & 31;
   const int64_t warp0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
@@ -250,7 +254,7 @@ static CastArgs make_args(const void* in, void* out, int64_t n, int format, int 
   a.seed_lo = (uint32_t)seed; a.seed_hi = (uint32_t)(seed >> 32);
   a.elem_offset = elem_offset;
   a.fmt = format; a.rnd = rounding; a.flags = flags;
-  a.d_amax = nullptr; a.flt_max = 0.0f; a.d_scale_out = nullptr;
+  a.d_amax = nullptr; a.flt_max = 0.0f; a.d_scale_out = nullptr; a.d_seed = seed_source();
   return a;
 }
 

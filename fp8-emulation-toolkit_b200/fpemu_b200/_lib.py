@@ -38,6 +38,8 @@ SIGNATURES = {
     "fpemu_cast_amax_scaled_fused": (_i32, [_vp, _vp, _i64, _i32, _i32, _i32, _i32, _f32, _vp, _i32, _u64, _u64, _vp]),
     "fpemu_encode_rowwise": (_i32, [_vp, _vp, _i64, _i64, _i32, _i32, _i32, _i32, _f32, _vp, _u64, _u64, _vp]),
     "fpemu_decode_rowwise": (_i32, [_vp, _vp, _i64, _i64, _i32, _i32, _i32, _vp, _vp]),
+    "fpemu_set_seed_source": (_i32, [_vp]),
+    "fpemu_advance_seed_source": (_i32, [_vp]),
     "fpemu_encode_multi": (_i32, [_vp, _vp, _i32, _i32, _i32, _i32, _vp, _u64, _vp]),
     "fpemu_encode": (_i32, [_vp, _vp, _i64, _i32, _i32, _i32, _i32, _f32, _vp, _u64, _u64, _vp]),
     "fpemu_decode": (_i32, [_vp, _vp, _i64, _i32, _i32, _i32, _f32, _vp, _vp]),

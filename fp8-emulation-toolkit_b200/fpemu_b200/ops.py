@@ -26,6 +26,40 @@ def next_seed():
     return (_seed_base << 32) | (next(_seed_counter) & 0xFFFFFFFF)
 
 
+_raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+_device_seeds = {}
+
+
+def enable_device_seed(device=None, value=0):
+    """Install a device-resident 64-bit word that every stochastic kernel on `device` adds to its seed
+    (fpemu_set_seed_source).  With `advance_device_seed()` captured in the same CUDA graph as the casts, every replay
+    of the graph draws fresh random bits; without a graph it is simply a seed offset that lives on the GPU."""
+    dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    word = torch.tensor([int(value)], dtype=torch.int64, device=dev)
+    with torch.cuda.device(dev):
+        L.check(L.lib().fpemu_set_seed_source(word.data_ptr()), "fpemu_set_seed_source")
+    _device_seeds[dev.index] = word                      # keeps the word alive
+    return word
+
+
+def disable_device_seed(device=None):
+    dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    with torch.cuda.device(dev):
+        L.check(L.lib().fpemu_set_seed_source(None), "fpemu_set_seed_source")
+    _device_seeds.pop(dev.index, None)
+
+
+def advance_device_seed(device=None):
+    """Enqueue (on the current stream) the one-thread kernel that moves the device seed word on."""
+    dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    if dev.index not in _device_seeds:
+        raise RuntimeError("fpemu: no device seed installed on %s (enable_device_seed first)" % dev)
+    with torch.cuda.device(dev):
+        st = L.lib().fpemu_advance_seed_source(_raw_stream(dev.index) if _raw_stream is not None
+                                               else torch.cuda.current_stream(dev).cuda_stream)
+    L.check(st, "fpemu_advance_seed_source")
+
+
 def _dt(t):
     try:
         return _DT[t.dtype]
@@ -38,9 +72,6 @@ def _check_tensor(t, name="input"):
         raise RuntimeError("%s must be a CUDA tensor" % name)           # CHECK_CUDA, cuda/fpemu_impl.cpp:23
     if not t.is_contiguous():
         raise RuntimeError("%s must be contiguous" % name)              # CHECK_CONTIGUOUS, :24
-
-
-_raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
 
 
 def _stream(t):

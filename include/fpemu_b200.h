@@ -92,6 +92,15 @@ FPEMU_API int fpemu_version(void);
 /* Text for a status returned by any entry point (static storage, never NULL). */
 FPEMU_API const char* fpemu_strerror(int status);
 
+/* Stochastic rounding under CUDA-graph replay.  The `seed` argument of every entry point is a host value: a captured
+ * graph would replay the same random bits forever.  fpemu_set_seed_source(d_seed) installs, for the CURRENT device, the
+ * address of a device-resident uint64 that every stochastic kernel adds to its seed when it starts (NULL removes it);
+ * fpemu_advance_seed_source(stream) enqueues a one-thread kernel that moves that word on.  Capture the advance together
+ * with the casts and every replay draws fresh bits; results stay a pure function of (seed + word, element index).
+ * Process-wide per-device setting, read when a call is made; deterministic modes never look at it. */
+FPEMU_API int fpemu_set_seed_source(const uint64_t* d_seed);
+FPEMU_API int fpemu_advance_seed_source(void* stream);
+
 /* Parse a reference mode string ("E4M3_RNE", "E5M2_DAZ_STOCHASTIC", "BFLOAT16_RNE", ...) into
  * (format, rounding, flags).  Replaces the `mode.compare(...)` chain of fpemu_cuda_forward,
  * fpemu_kernels.cu:1058-1364.  Besides the reference's strings it accepts <FMT>_RTZ for E4M3, E3M4,
