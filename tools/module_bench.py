@@ -137,6 +137,41 @@ def main():
     qutils.set_output_cast_out_of_place(False)
     out["bert_base_hybrid_step_out_of_place_outputs"] = {"emulated_step_ms": emul_oop, "cast_kernel_ms_per_step": ours_oop,
                                                          "all_kernel_ms_per_step": total_oop, "cast_launches_per_step": n_oop}
+    # the whole emulated training step as ONE CUDA graph: the library neither synchronises nor allocates, the hooks are
+    # sync-free, and the device seed word gives the stochastic gradient casts fresh bits on every replay
+    try:
+        import fpemu_b200 as F
+        qutils.set_output_cast_out_of_place(True)
+        F.enable_device_seed(value=1)
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(3):
+                estep()
+                F.advance_device_seed()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        opt.zero_grad(set_to_none=True)
+        with torch.cuda.graph(graph):
+            loss = bert(input_ids=ids, start_positions=sp, end_positions=ep).loss
+            loss.backward()
+            emu.optimizer_step(opt)
+            F.advance_device_seed()
+        losses = []
+        for _ in range(3):
+            graph.replay()
+            losses.append(float(loss))
+        graph_ms = timed(graph.replay)
+        out["bert_base_hybrid_step_one_cuda_graph"] = {"replay_ms": graph_ms, "losses_of_3_replays": losses}
+    except Exception as e:  # noqa: BLE001
+        out["bert_base_hybrid_step_one_cuda_graph"] = {"failed": "%s: %s" % (type(e).__name__, str(e)[:300])}
+    finally:
+        qutils.set_output_cast_out_of_place(False)
+        try:
+            F.disable_device_seed()
+        except Exception:  # noqa: BLE001
+            pass
     out["bert_base_hybrid_step"] = {"batch": args.bert_batch, "seq": args.bert_seq, "fp32_step_ms": base, "emulated_step_ms": emul,
                                     "cast_kernel_ms_per_step": ours, "all_kernel_ms_per_step": total, "cast_launches_per_step": n}
     print(json.dumps(out, indent=1))
