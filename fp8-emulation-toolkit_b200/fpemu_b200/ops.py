@@ -33,7 +33,9 @@ _device_seeds = {}
 def enable_device_seed(device=None, value=0):
     """Install a device-resident 64-bit word that every stochastic kernel on `device` adds to its seed
     (fpemu_set_seed_source).  With `advance_device_seed()` captured in the same CUDA graph as the casts, every replay
-    of the graph draws fresh random bits; without a graph it is simply a seed offset that lives on the GPU."""
+    of the graph draws fresh random bits; without a graph it is simply a seed offset that lives on the GPU.
+    Returns the int64 tensor holding the word: a captured graph keeps its address, so set a new value with
+    `word.fill_(v)` rather than calling this again."""
     dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
     word = torch.tensor([int(value)], dtype=torch.int64, device=dev)
     with torch.cuda.device(dev):

@@ -97,7 +97,8 @@ FPEMU_API const char* fpemu_strerror(int status);
  * address of a device-resident uint64 that every stochastic kernel adds to its seed when it starts (NULL removes it);
  * fpemu_advance_seed_source(stream) enqueues a one-thread kernel that moves that word on.  Capture the advance together
  * with the casts and every replay draws fresh bits; results stay a pure function of (seed + word, element index).
- * Process-wide per-device setting, read when a call is made; deterministic modes never look at it. */
+ * Process-wide per-device setting, read when a call is made (a captured graph keeps the address it was captured with:
+ * keep that word alive and change its VALUE, not its address, afterwards); deterministic modes never look at it. */
 FPEMU_API int fpemu_set_seed_source(const uint64_t* d_seed);
 FPEMU_API int fpemu_advance_seed_source(void* stream);
 

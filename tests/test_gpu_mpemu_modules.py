@@ -271,6 +271,66 @@ def test_master_parameter_requantization_is_one_multi_tensor_launch(mp):
     assert calls == [("FLOAT16_STOCHASTIC", 4), ("FLOAT16_STOCHASTIC", 4)]              # one launch per step, 4 tensors
 
 
+def test_emulated_training_step_as_one_cuda_graph(mp):
+    """Forward, backward (with the E5M2-stochastic gradient hooks) and optimizer step captured once and replayed:
+    nothing in the hook layer or the library synchronises or allocates outside the graph's pool.  Two identically
+    initialised models are trained with identical seeds (host counter reset before every step, device seed word set
+    to the step number), one eagerly and one by replaying the graph; their weights must end up bit-identical."""
+    from mpemu import mpt_emu, qutils
+    import fpemu_b200 as F
+
+    def build():
+        torch.manual_seed(0)
+        model = torch.nn.Sequential(torch.nn.Linear(128, 256), torch.nn.GELU(), torch.nn.Linear(256, 64)).cuda().train()
+        opt = torch.optim.SGD(model.parameters(), lr=0.05)
+        model, emu = mpt_emu.initialize(model, None, training_algo="hybrid", device="cuda")
+        return model, opt, emu
+
+    g = torch.Generator(device="cuda").manual_seed(5)
+    x = torch.randn(32, 16, 128, device="cuda", generator=g)
+    target = torch.randn(32, 16, 64, device="cuda", generator=g)
+    qutils.set_output_cast_out_of_place(True)
+    word = F.enable_device_seed(value=0)
+    try:
+        def make_step(model, opt, emu):
+            def step():
+                opt.zero_grad(set_to_none=True)
+                loss = torch.nn.functional.mse_loss(model(x), target)
+                loss.backward()
+                emu.optimizer_step(opt)
+                return loss
+            return step
+        ma, oa, ea = build()
+        mb, ob, eb = build()
+        step_a, step_b = make_step(ma, oa, ea), make_step(mb, ob, eb)
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for k in range(3):                                            # warm-up, identical for both models
+                for st in (step_a, step_b):
+                    F.manual_seed(100)
+                    word.fill_(k)
+                    st()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        oa.zero_grad(set_to_none=True)
+        F.manual_seed(100)
+        with torch.cuda.graph(graph):
+            loss_a = step_a()
+        for k in range(3, 9):
+            word.fill_(k)
+            graph.replay()
+            F.manual_seed(100)
+            loss_b = step_b()
+            assert float(loss_a) == float(loss_b), "step %d" % k
+        for pa, pb in zip(ma.parameters(), mb.parameters()):
+            assert torch.equal(pa.detach().view(torch.int32), pb.detach().view(torch.int32))
+    finally:
+        qutils.set_output_cast_out_of_place(False)
+        F.disable_device_seed()
+
+
 def test_fpemuop_autograd_contract(mp):
     """FPEmuOp: 'NONE' passes through, straight-through gradient, mark_dirty on in-place, sparse values path."""
     from mpemu.pytquant.cuda.fpemu import FPEmuOp
