@@ -138,6 +138,75 @@ __global__ void __launch_bounds__(256) decode_rows_generic_kernel(const CastArgs
   }
 }
 
+// Row-wise cast with scales the caller supplies (one float per row): the value-to-value counterpart of decode_rows_kernel.
+// Used where the reference derives a per-channel scale from something other than the maximum (its `mean` scaling
+// takes torch.mode of each channel, mpemu/qutils.py:294-301).
+template <int FMT, int RND, int DT>
+__global__ void __launch_bounds__(kThreads) cast_rows_scaled_kernel(const CastArgs a_, const int64_t vpr, const float* d_row_scale) {
+  const CastArgs a = with_device_seed(a_);
+  constexpr int VE = DtInfo<DT>::kVecElems;
+  constexpr int U = UnrollFor<DT>::value;
+  const int64_t nvec = a.n / VE;
+  const char* in = static_cast<const char*>(a.in);
+  char* out = static_cast<char*>(a.out);
+  const int64_t base = (int64_t)blockIdx.x * (kThreads * U) + threadIdx.x;
+  Vec32 v[U];
+  float s[U];
+#pragma unroll
+  for (int j = 0; j < U; ++j) {
+    const int64_t vi = base + j * kThreads;
+    s[j] = 1.0f;
+    if (vi < nvec) {
+      v[j] = ldg256(in + vi * 32);
+      s[j] = __ldg(d_row_scale + vi / vpr);
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < U; ++j) {
+    const int64_t vi = base + j * kThreads;
+    if (vi < nvec) {
+      ScaleCtx sc;
+      sc.scale = effective_scale(s[j], DT);
+      sc.rscale = __frcp_rn(sc.scale);
+      sc.unscale32 = (a.flags & FPEMU_FLAG_UNSCALE_FP32) != 0;
+      process_vec<FMT, RND, false, DT, true>(v[j], sc, a, a.elem_offset + (uint64_t)vi * VE);
+      stg256(out + vi * 32, v[j]);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) cast_rows_scaled_generic_kernel(const CastArgs a_, const int64_t cols, const int dt,
+                                                                      const float* d_row_scale) {
+  const CastArgs a = with_device_seed(a_);
+  const bool wide = (a.fmt == FPEMU_FMT_BF16 || a.fmt == FPEMU_FMT_FP16);
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < a.n; i += stride) {
+    const float s = effective_scale(__ldg(d_row_scale + i / cols), dt);
+    uint32_t rb = 0u;
+    if (a.rnd == FPEMU_RND_STOCHASTIC) rb = rand_bits_one(a.seed_lo, a.seed_hi, a.elem_offset + (uint64_t)i, wide);
+    store_elem(a.out, i, dt, cast_one(load_elem(a.in, i, dt), a.fmt, a.rnd, a.flags, true, s, __frcp_rn(s), dt == FPEMU_DT_F16, rb));
+  }
+}
+
+typedef void (*RowsScaledKernel)(const CastArgs, const int64_t, const float*);
+template <int FMT, int RND>
+static RowsScaledKernel rs_dt(int dt) {
+  switch (dt) {
+    case FPEMU_DT_F32:  return cast_rows_scaled_kernel<FMT, RND, FPEMU_DT_F32>;
+    case FPEMU_DT_F16:  return cast_rows_scaled_kernel<FMT, RND, FPEMU_DT_F16>;
+    default:            return cast_rows_scaled_kernel<FMT, RND, FPEMU_DT_BF16>;
+  }
+}
+template <int FMT>
+static RowsScaledKernel rs_rnd(int rnd, int dt) {
+  switch (rnd) {
+    case FPEMU_RND_RNE:        return rs_dt<FMT, FPEMU_RND_RNE>(dt);
+    case FPEMU_RND_RTZ:        return rs_dt<FMT, FPEMU_RND_RTZ>(dt);
+    case FPEMU_RND_STOCHASTIC: return rs_dt<FMT, FPEMU_RND_STOCHASTIC>(dt);
+    default:                   return nullptr;
+  }
+}
+
 typedef void (*EncRowsKernel)(const CastArgs, const int64_t, const int, const int, const bool, const float, float*);
 typedef void (*DecRowsKernel)(const CastArgs, const int64_t, const float*);
 
@@ -259,5 +328,38 @@ extern "C" int fpemu_decode_rowwise(const void* codes, void* out, int64_t rows, 
   int64_t want = (n + 255) / 256;
   const int64_t cap = (int64_t)device_info().sm_count * 8;
   decode_rows_generic_kernel<<<(int)(want < cap ? want : cap), 256, 0, stream>>>(a, cols, dtype, d_row_scale);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int fpemu_cast_rows_scaled(const void* in, void* out, int64_t rows, int64_t cols, int dtype, int format,
+                                      int rounding, int flags, const float* d_row_scale, uint64_t seed,
+                                      uint64_t elem_offset, void* stream_) {
+  using namespace fpemu;
+  int st = validate_rows(in, out, d_row_scale, rows, cols, dtype, format, rounding);
+  if (st != FPEMU_OK) return st;
+  if ((uintptr_t)out % (uintptr_t)dtype_bytes(dtype)) return FPEMU_ERR_ALIGN;
+  const int64_t n = rows * cols;
+  if (n == 0) return FPEMU_OK;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  const CastArgs a = rows_args(in, out, n, format, rounding, flags, seed, elem_offset);
+  const int ve = dtype == FPEMU_DT_F32 ? 8 : 16;
+  const bool aligned = (((uintptr_t)in | (uintptr_t)out) & 31u) == 0 && cols % ve == 0;
+  const bool rng_ok = (rounding != FPEMU_RND_STOCHASTIC) || ((elem_offset & 15u) == 0);
+  RowsScaledKernel k = nullptr;
+  if (aligned && rng_ok && !(flags & FPEMU_FLAG_DAZ)) {
+    k = format == FPEMU_FMT_E5M2 ? rs_rnd<FPEMU_FMT_E5M2>(rounding, dtype)
+      : format == FPEMU_FMT_E4M3 ? rs_rnd<FPEMU_FMT_E4M3>(rounding, dtype) : rs_rnd<FPEMU_FMT_E3M4>(rounding, dtype);
+  }
+  if (k != nullptr) {
+    const int u = dtype == FPEMU_DT_F32 ? UnrollFor<FPEMU_DT_F32>::value : UnrollFor<FPEMU_DT_F16>::value;
+    const int64_t per_cta = (int64_t)kThreads * u;
+    const int64_t grid = (n / ve + per_cta - 1) / per_cta;
+    if (grid > 0x7FFFFFFFLL) return FPEMU_ERR_TOO_LARGE;
+    k<<<(unsigned)grid, kThreads, 0, stream>>>(a, cols / ve, d_row_scale);
+    return (int)cudaGetLastError();
+  }
+  int64_t want = (n + 255) / 256;
+  const int64_t cap = (int64_t)device_info().sm_count * 8;
+  cast_rows_scaled_generic_kernel<<<(int)(want < cap ? want : cap), 256, 0, stream>>>(a, cols, dtype, d_row_scale);
   return (int)cudaGetLastError();
 }

@@ -36,6 +36,7 @@ SIGNATURES = {
     "fpemu_cast_host": (_i32, [_vp, _vp, _i64, _i32, _i32, _i32, _i32, _f32, _u64, _vp, _vp, _i64, _vp, _vp, _vp]),
     "fpemu_fused_work_floats": (_i32, []),
     "fpemu_cast_amax_scaled_fused": (_i32, [_vp, _vp, _i64, _i32, _i32, _i32, _i32, _f32, _vp, _i32, _u64, _u64, _vp]),
+    "fpemu_cast_rows_scaled": (_i32, [_vp, _vp, _i64, _i64, _i32, _i32, _i32, _i32, _vp, _u64, _u64, _vp]),
     "fpemu_encode_rowwise": (_i32, [_vp, _vp, _i64, _i64, _i32, _i32, _i32, _i32, _f32, _vp, _u64, _u64, _vp]),
     "fpemu_decode_rowwise": (_i32, [_vp, _vp, _i64, _i64, _i32, _i32, _i32, _vp, _vp]),
     "fpemu_set_seed_source": (_i32, [_vp]),

@@ -361,6 +361,33 @@ def cast_rowwise(x2d, mode, out=None, flt_max=None, clamp=True, seed=None, elem_
     return (out, scales) if return_scales else out
 
 
+def cast_rows_scaled(x2d, mode, scales, out=None, seed=None, elem_offset=0, unscale_fp32=False, rows=None, cols=None):
+    """Row r of `x2d` cast with scale `scales[r]` (float32 CUDA vector, read on the device): one launch for a whole
+    per-channel loop whose scales are not the row maxima."""
+    _check_tensor(x2d)
+    fmt, rnd, flags = L.parse_mode(mode)
+    if unscale_fp32:
+        flags |= L.FLAG_UNSCALE_FP32
+    if rows is None:
+        rows = x2d.shape[0] if x2d.dim() > 0 else 1
+        cols = x2d.numel() // max(rows, 1)
+    if not (scales.is_cuda and scales.dtype == torch.float32 and scales.is_contiguous() and scales.numel() >= rows):
+        raise ValueError("fpemu: scales must be a contiguous float32 CUDA tensor with one entry per row")
+    if out is None:
+        out = torch.empty_like(x2d)
+    else:
+        _check_tensor(out, "out")
+        if out.dtype != x2d.dtype or out.numel() < rows * cols:
+            raise ValueError("fpemu: out must match input dtype and size")
+    if rnd == L.RND_STOCHASTIC and seed is None:
+        seed = next_seed()
+    with _on_device(x2d):
+        st = L.lib().fpemu_cast_rows_scaled(x2d.data_ptr(), out.data_ptr(), int(rows), int(cols), _dt(x2d), fmt, rnd, flags,
+                                            scales.data_ptr(), int(seed or 0), int(elem_offset), _stream(x2d))
+    L.check(st, "fpemu_cast_rows_scaled(%s)" % mode)
+    return out
+
+
 def encode_rowwise(x2d, mode, codes=None, scales=None, flt_max=None, clamp=True, seed=None, elem_offset=0, rows=None,
                    cols=None):
     """Per-channel wire form: (codes uint8 of x2d's shape, scales float32[rows]) such that

@@ -276,12 +276,27 @@ def quantize_tensor(tensor, qtconfig, qtparams, inplace=False):
         channels = tensor.shape[0]
         cols = tensor.numel() // max(channels, 1)
         if qtconfig.scaling_method == "mean":
-            # the reference takes the *mode* of each channel here (:297); rare path, kept in torch
+            # the reference takes the *mode* of each channel here (:297) and calls the op once per channel.  Same
+            # numbers from ONE torch.mode over dim 1 (checked equal to the per-channel calls, ties included), the
+            # scale expression of :298-301 on the device, and one row-wise launch with those scales: no .item().
+            flt_min = qtconfig.get_flt_min()
+            if takes_scale and _supported_dtype(tensor) and channels > 0 and cols > 0:
+                src = tensor.detach()
+                src = src if src.is_contiguous() else src.contiguous()
+                m = torch.abs(torch.mode(src.reshape(channels, cols), dim=1).values).float()
+                m = torch.where(m > 1e-6, m, torch.full_like(m, flt_min))
+                scales = torch.clamp(flt_min / m, min=1.0).contiguous()
+                out = src if (inplace and src.data_ptr() == tensor.data_ptr()) else torch.empty_like(src)
+                _F.cast_rows_scaled(src, mode, scales, out=out, rows=channels, cols=cols, unscale_fp32=_UNSCALE_FP32)
+                if inplace and out.data_ptr() != tensor.data_ptr():
+                    tensor.copy_(out)
+                    return tensor
+                return tensor if inplace else out
             out = tensor if inplace else torch.zeros_like(tensor)
             for c in range(channels):
                 sub = tensor.select(0, c).detach()
                 m = abs(torch.mode(torch.flatten(sub)).values.item())
-                scale = _mean_scale(m, qtconfig.get_flt_min(), 1e-6)
+                scale = _mean_scale(m, flt_min, 1e-6)
                 out.select(0, c).data.copy_(fpemu_device_fn(sub, mode, inplace=False, scale=scale))
             return out
         if takes_scale and _supported_dtype(tensor):

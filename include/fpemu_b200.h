@@ -203,6 +203,14 @@ FPEMU_API int fpemu_encode_rowwise(const void* in, void* codes, int64_t rows, in
 FPEMU_API int fpemu_decode_rowwise(const void* codes, void* out, int64_t rows, int64_t cols, int dtype, int format,
                          int flags, const float* d_row_scale, void* stream);
 
+/* Row-wise cast with caller-supplied scales: row r is cast with scale d_row_scale[r] (read on the device, no host sync).
+ * For per-channel scales that are not derived from the row maximum — the reference's per-channel `mean` scaling takes
+ * torch.mode of each channel and calls the op once per channel (mpemu/qutils.py:289-311 with :294-301); this is that
+ * loop as one launch.  Vector path: buffers 32-byte aligned, cols a multiple of 8 (float32) / 16 (16-bit). */
+FPEMU_API int fpemu_cast_rows_scaled(const void* in, void* out, int64_t rows, int64_t cols, int dtype, int format,
+                           int rounding, int flags, const float* d_row_scale, uint64_t seed, uint64_t elem_offset,
+                           void* stream);
+
 /* Host-buffer convenience used by the end-to-end measurement: casts n elements that live in HOST
  * memory (pinned for full speed) into a HOST output, staging through two caller-provided device
  * buffers of chunk_elems elements each (d_stage[0], d_stage[1]) so the H2D copy, the kernel and the

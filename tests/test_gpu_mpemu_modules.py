@@ -331,6 +331,34 @@ def test_emulated_training_step_as_one_cuda_graph(mp):
         F.disable_device_seed()
 
 
+@pytest.mark.parametrize("shape", [(64, 64, 3, 3), (16, 3, 3, 3), (128, 256), (5, 1000)])
+def test_per_channel_mean_scaling_in_one_launch_equals_the_per_channel_loop(mp, shape):
+    """E5M2's default weight config is "per-channel-mean": the reference takes torch.mode of every channel and calls the
+    op once per channel (qutils.py:289-311).  Here: one batched torch.mode, scales derived on the device, one
+    row-wise launch — bit-identical to that loop."""
+    from mpemu import qutils
+    import fpemu_b200 as F
+    g = torch.Generator(device="cuda").manual_seed(sum(shape))
+    w = torch.randn(shape, device="cuda", generator=g) * 0.05
+    w.view(shape[0], -1)[0, :4] = 0.125                               # a channel with a real mode
+    w.view(shape[0], -1)[1] = 0.0                                     # an all-zero channel: mode 0 -> floor -> flt_min
+    cfg = qutils.TensorQuantConfig("e5m2", "rne", "per-channel-mean")
+    got = qutils.quantize_tensor(w, cfg, None, inplace=False)
+    flt_min = cfg.get_flt_min()
+    want = torch.empty_like(w)
+    for c in range(shape[0]):
+        sub = w.select(0, c)
+        mean = abs(torch.mode(torch.flatten(sub)).values)
+        mean = abs(mean) if abs(mean) > 1e-6 else flt_min
+        scale = flt_min / abs(mean)
+        scale = 1.0 if scale < 1.0 else scale
+        want.select(0, c).copy_(F.cast(sub.contiguous(), "E5M2_RNE", scale=float(scale), unscale_fp32=True))
+    assert torch.equal(got.view(torch.int32), want.view(torch.int32))
+    w2 = w.clone()
+    assert qutils.quantize_tensor(w2, cfg, None, inplace=True) is w2
+    assert torch.equal(w2.view(torch.int32), want.view(torch.int32))
+
+
 def test_fpemuop_autograd_contract(mp):
     """FPEmuOp: 'NONE' passes through, straight-through gradient, mark_dirty on in-place, sparse values path."""
     from mpemu.pytquant.cuda.fpemu import FPEmuOp
