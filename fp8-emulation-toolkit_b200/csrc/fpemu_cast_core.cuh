@@ -232,6 +232,32 @@ __device__ __forceinline__ void process_vec(Vec32& v, const ScaleCtx& sc, const 
       r0 = philox4x32_10(a.seed_lo, a.seed_hi, g0 >> 3);
       if (kPairs > 4) r1 = philox4x32_10(a.seed_lo, a.seed_hi, (g0 >> 3) + 1);
     }
+    if (kSR && DT != FPEMU_DT_F16) {
+      // Stochastic FLOAT16 of fp32 / bf16 values (fpemu_kernels.cu:340-372): inside the fp16 normal range
+      // [2^-14, 2^16) the reference adds 13 random bits under the kept mantissa and truncates — done here on the fp32
+      // encoding, after which the conversion to fp16 is exact (a carry up to 2^16 converts to Inf exactly as the
+      // reference's exponent carry does); everything else (fp16-subnormal range: plain RNE; >= 2^16 and Inf: Inf)
+      // is what cvt.rn.f16.f32 does by itself.  NaN keeps sign and payload in the reference but not in the
+      // hardware conversion: vectors holding a NaN take the element-wise code below.
+      uint32_t nan_any = 0u, hp[kPairs];
+#pragma unroll
+      for (int k = 0; k < kPairs; ++k) {
+        const uint4& rr = (k < 4) ? r0 : r1;
+        const int wsel = k & 3;
+        const uint32_t rbits = wsel == 0 ? rr.x : (wsel == 1 ? rr.y : (wsel == 2 ? rr.z : rr.w));
+        const float2 f = get_pair<DT>(v, k);
+        uint32_t u0 = __float_as_uint(f.x), u1 = __float_as_uint(f.y);
+        if (((u0 & 0x7FFFFFFFu) - 0x38800000u) < 0x0F000000u) u0 = (u0 + (rbits & 0x1FFFu)) & 0xFFFFE000u;
+        if (((u1 & 0x7FFFFFFFu) - 0x38800000u) < 0x0F000000u) u1 = (u1 + ((rbits >> 16) & 0x1FFFu)) & 0xFFFFE000u;
+        hp[k] = pack_f16x2_rn(__uint_as_float(u0), __uint_as_float(u1));
+        nan_any |= __hneu2_mask(as_h2(hp[k]), as_h2(hp[k]));
+      }
+      if (nan_any == 0u) {
+#pragma unroll
+        for (int k = 0; k < kPairs; ++k) put_pair<DT>(v, k, unpack_f16x2(hp[k]));
+        return;
+      }
+    }
 #pragma unroll
     for (int k = 0; k < kPairs; ++k) {
       const uint4& rr = (k < 4) ? r0 : r1;
