@@ -587,3 +587,36 @@ def test_single_launch_amax_scaled_cast_in_a_cuda_graph(F):
     graph.replay()
     torch.cuda.synchronize()
     assert torch.equal(y.view(torch.int32), want.view(torch.int32))
+
+
+def test_concurrent_host_threads_on_their_own_streams(F):
+    """Four host threads, each with its own stream and tensors, hammer the entry points at once (ctypes drops the GIL
+    during a call): per-device caches inside the library are lock-protected, per-call state lives in the arguments."""
+    import threading
+    xs = [dev(wide(200003, 60 + i)) for i in range(4)]
+    want = [(F.cast(x, "E4M3_STOCHASTIC", seed=5 + i).clone(), F.cast_amax_scaled(x, "E4M3_RNE", fused=True).clone(),
+             F.encode(x, "E5M2_RNE").clone()) for i, x in enumerate(xs)]
+    torch.cuda.synchronize()
+    errors = []
+
+    def worker(i):
+        try:
+            s = torch.cuda.Stream()
+            with torch.cuda.stream(s):
+                for _ in range(100):
+                    a = F.cast(xs[i], "E4M3_STOCHASTIC", seed=5 + i)
+                    b = F.cast_amax_scaled(xs[i], "E4M3_RNE")
+                    c = F.encode(xs[i], "E5M2_RNE")
+                s.synchronize()
+                bits = torch.int32
+                if not (torch.equal(a.view(bits), want[i][0].view(bits)) and torch.equal(b.view(bits), want[i][1].view(bits))
+                        and torch.equal(c, want[i][2])):
+                    errors.append("thread %d: results differ" % i)
+        except Exception as e:  # noqa: BLE001
+            errors.append("thread %d: %r" % (i, e))
+    threads = [threading.Thread(target=worker, args=(i,)) for i in range(4)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join(timeout=120)
+    assert not errors, errors
