@@ -258,6 +258,26 @@ int launch_cast(const CastArgs& a, int dtype, cudaStream_t stream) {
   const bool rng_ok = (a.rnd != FPEMU_RND_STOCHASTIC) || ((a.elem_offset & 15u) == 0);
   CastKernel k = (aligned && rng_ok) ? pick_kernel(a.fmt, a.rnd, daz, dtype, scaled) : nullptr;
   const int sms = device_info().sm_count;
+  // A view that starts off a 32-byte boundary (a slice of a flat parameter buffer, x[1:]), input and output off by the
+  // same amount: the few elements up to the boundary go through the element-wise kernel, the rest is an aligned
+  // problem for the vector kernels — provided the random stream lines up there too.
+  const uintptr_t mis = (uintptr_t)a.in & 31u;
+  if (!aligned && mis == ((uintptr_t)a.out & 31u)) {
+    const int esz = dtype_bytes(dtype);
+    const int64_t head = (int64_t)((32u - mis) / (uintptr_t)esz);
+    const bool body_rng_ok = (a.rnd != FPEMU_RND_STOCHASTIC) || (((a.elem_offset + (uint64_t)head) & 15u) == 0);
+    if (head < a.n && body_rng_ok && pick_kernel(a.fmt, a.rnd, daz, dtype, scaled) != nullptr) {
+      CastArgs h = a;
+      h.n = head;
+      cast_generic_kernel<<<1, 32, 0, stream>>>(h, dtype);
+      CastArgs b = a;
+      b.in = static_cast<const char*>(a.in) + head * esz;
+      b.out = static_cast<char*>(a.out) + head * esz;
+      b.n = a.n - head;
+      b.elem_offset = a.elem_offset + (uint64_t)head;
+      return launch_cast(b, dtype, stream);
+    }
+  }
   if (k != nullptr) {
     const int ve = dtype == FPEMU_DT_F32 ? 8 : 16;
     const int u = dtype == FPEMU_DT_F32 ? UnrollFor<FPEMU_DT_F32>::value : UnrollFor<FPEMU_DT_F16>::value;
