@@ -100,6 +100,20 @@ class _on_device(object):
             torch.cuda.set_device(self.prev)
 
 
+def empty_like_coaligned(x):
+    """torch.empty_like(x), except that for a view starting off a 32-byte boundary the result starts off by the same
+    amount (it is then a view into a slightly larger allocation): input and output misaligned alike is the case the
+    vector kernels handle at full speed, an aligned output for a misaligned input is not."""
+    mis = x.data_ptr() & 31
+    esz = x.element_size()
+    if mis == 0 or mis % esz or not x.is_contiguous():
+        return torch.empty_like(x)
+    k = mis // esz
+    buf = torch.empty(x.numel() + 32 // esz, dtype=x.dtype, device=x.device)
+    k = (k - (buf.data_ptr() & 31) // esz) % (32 // esz)
+    return buf[k:k + x.numel()].view(x.shape)
+
+
 def cast(x, mode, out=None, scale=1.0, d_scale=None, seed=None, elem_offset=0, n=None, unscale_fp32=False):
     """QDQ-cast `x` (CUDA, contiguous) into `out` (default: new tensor; pass out=x for in-place).
     `d_scale`: optional 1-element float32 CUDA tensor used instead of `scale` (no host sync)."""
@@ -108,7 +122,7 @@ def cast(x, mode, out=None, scale=1.0, d_scale=None, seed=None, elem_offset=0, n
     if unscale_fp32:
         flags |= L.FLAG_UNSCALE_FP32
     if out is None:
-        out = torch.empty_like(x)
+        out = empty_like_coaligned(x)
     else:
         _check_tensor(out, "out")
         if out.dtype != x.dtype or out.numel() < (x.numel() if n is None else n):

@@ -43,7 +43,7 @@ def forward(input, mode, size, inplace, scale, block_norm, block_size):
     elif size < x.numel():
         out = torch.zeros_like(x)          # elements past `size` stay zero like the reference's zeros_like (:1044)
     else:
-        out = torch.empty_like(x)          # every element is written: no memset pass
+        out = ops.empty_like_coaligned(x)  # every element is written: no memset pass; a view gets an equally aligned output
     host_scale, d_scale = _scale_args(scale)
     blocked = bool(block_norm)
     # block_norm is honoured only by the E5M2 / E4M3 / E4M3_IEEE / E3M4 / FP4 kernels (fpemu_kernels.cu:1058-1364)

@@ -620,3 +620,21 @@ def test_concurrent_host_threads_on_their_own_streams(F):
     for t in threads:
         t.join(timeout=120)
     assert not errors, errors
+
+
+def test_out_of_place_cast_of_a_view_gets_an_equally_aligned_output(F):
+    """x[1:] starts 4 bytes off a 32-byte boundary; the output the library allocates starts off by the same amount so
+    that the vector kernels run (input and output misaligned alike), and holds the right values."""
+    import fpemu_cuda
+    for dt in (torch.float32, torch.bfloat16, torch.float16):
+        base = torch.randn(100003, device="cuda").to(dt)
+        for off in (1, 3, 8, 13):
+            x = base[off:]
+            y = F.cast(x, "E4M3_RNE")
+            assert y.data_ptr() % 32 == x.data_ptr() % 32 and y.shape == x.shape and y.is_contiguous()
+            want = F.cast(x.clone(), "E4M3_RNE")                      # aligned copy of the same values
+            bits = torch.int32 if dt == torch.float32 else torch.int16
+            assert torch.equal(y.view(bits), want.view(bits))
+            z = fpemu_cuda.forward(x, "E5M2_RNE", x.numel(), False, 1.0, False, 1)[0]
+            assert z.data_ptr() % 32 == x.data_ptr() % 32
+            assert torch.equal(z.view(bits), F.cast(x.clone(), "E5M2_RNE").view(bits))
