@@ -268,7 +268,6 @@ extern "C" int fpemu_amax(const void* in, int64_t n, int dtype, float* d_amax, v
   if ((uintptr_t)in % (uintptr_t)dtype_bytes(dtype)) return FPEMU_ERR_ALIGN;
   if (n == 0) return FPEMU_OK;
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-  const int sms = device_info().sm_count;
   if (((uintptr_t)in & 31u) == 0) {
     const int ve = dtype == FPEMU_DT_F32 ? 8 : 16;
     const int64_t per_cta = (int64_t)kAmaxThreads * kAmaxUnroll;
@@ -282,9 +281,12 @@ extern "C" int fpemu_amax(const void* in, int64_t n, int dtype, float* d_amax, v
       default:            amax_kernel<FPEMU_DT_BF16><<<grid, kAmaxThreads, 0, stream>>>(in, n, d_amax); break;
     }
   } else {
-    int64_t want = (n + 255) / 256;
-    const int64_t cap = (int64_t)sms * 8;
-    amax_generic_kernel<<<(int)(want < cap ? want : cap), 256, 0, stream>>>(in, n, dtype, d_amax);
+    // a view off a 32-byte boundary: the elements up to the boundary go through the scalar kernel, the rest is aligned
+    const int esz = dtype_bytes(dtype);
+    const int64_t head = (int64_t)((32u - ((uintptr_t)in & 31u)) / (uintptr_t)esz);
+    const int64_t first = head < n ? head : n;
+    amax_generic_kernel<<<1, 32, 0, stream>>>(in, first, dtype, d_amax);
+    if (first < n) return fpemu_amax(static_cast<const char*>(in) + first * esz, n - first, dtype, d_amax, stream_);
   }
   return (int)cudaGetLastError();
 }
