@@ -71,8 +71,7 @@ __global__ void __launch_bounds__(256) cast_generic_kernel(const CastArgs a_, co
   if (scaled) {
     s = a.d_scale ? __ldg(a.d_scale) : a.scale;
     if (a.d_amax != nullptr) {
-      s = __fdiv_rn(a.flt_max, __ldg(a.d_amax));
-      if (s > 3.275e4f) s = 6.55e4f;
+      s = scale_from_amax(__ldg(a.d_amax), a.flt_max, true, dt);
       if (a.d_scale_out != nullptr && blockIdx.x == 0 && threadIdx.x == 0) *a.d_scale_out = s;
     }
     s = effective_scale(s, dt);
@@ -105,8 +104,7 @@ __global__ void __launch_bounds__(kThreads) cast_vec_generic_kernel(const CastAr
   if (scaled) {
     s = a.d_scale ? __ldg(a.d_scale) : a.scale;
     if (a.d_amax != nullptr) {
-      s = __fdiv_rn(a.flt_max, __ldg(a.d_amax));
-      if (s > 3.275e4f) s = 6.55e4f;
+      s = scale_from_amax(__ldg(a.d_amax), a.flt_max, true, DT);
       if (a.d_scale_out != nullptr && blockIdx.x == 0 && threadIdx.x == 0) *a.d_scale_out = s;
     }
     s = effective_scale(s, DT);
@@ -243,7 +241,7 @@ int validate_cast(int64_t n, int dtype, int format, int rounding, float scale, c
   if (dtype < 0 || dtype >= FPEMU_DT_COUNT) return FPEMU_ERR_DTYPE;
   if (format < 0 || format >= FPEMU_FMT_COUNT || rounding < 0 || rounding >= FPEMU_RND_COUNT) return FPEMU_ERR_MODE;
   if (format == FPEMU_FMT_FP16 && rounding != FPEMU_RND_RNE && rounding != FPEMU_RND_STOCHASTIC) return FPEMU_ERR_MODE;
-  if (!(scale <= 65504.0f)) return FPEMU_ERR_SCALE;             // also rejects NaN
+  if (scale > 65504.0f) return FPEMU_ERR_SCALE;                 // `if (scale > 65504)`, :1037: a NaN scale passes, as there
   if (n > 0 && (in == nullptr || out == nullptr)) return FPEMU_ERR_ARG;
   const uintptr_t esz = (uintptr_t)dtype_bytes(dtype);
   if (((uintptr_t)in % esz) || ((uintptr_t)out % esz)) return FPEMU_ERR_ALIGN;

@@ -95,7 +95,7 @@ __device__ __forceinline__ void process_vec_bf16(Vec32& v, const CastArgs& a, ui
 }
 
 // Scale set-up shared by the vector kernels: host scalar, device scalar, or derived from a device-resident
-// absolute maximum (scale = clamp(flt_max / *d_amax), mpemu/qutils.py:283-285).
+// absolute maximum (scale_from_amax(), mpemu/qutils.py:283-285).
 template <int DT, bool SCALED>
 __device__ __forceinline__ ScaleCtx make_scale_ctx(const CastArgs& a) {
   ScaleCtx sc;
@@ -104,8 +104,7 @@ __device__ __forceinline__ ScaleCtx make_scale_ctx(const CastArgs& a) {
   if (SCALED) {
     float s = a.d_scale ? __ldg(a.d_scale) : a.scale;
     if (a.d_amax != nullptr) {                // per-tensor amax-scaled cast without a separate scale launch
-      s = __fdiv_rn(a.flt_max, __ldg(a.d_amax));
-      if (s > 3.275e4f) s = 6.55e4f;
+      s = scale_from_amax(__ldg(a.d_amax), a.flt_max, true, DT);
       if (a.d_scale_out != nullptr && blockIdx.x == 0 && threadIdx.x == 0) *a.d_scale_out = s;
     }
     s = effective_scale(s, DT);

@@ -151,7 +151,7 @@ static int validate_codec(const void* wide, const void* codes, int64_t n, int dt
   if (dtype < 0 || dtype >= FPEMU_DT_COUNT) return FPEMU_ERR_DTYPE;
   if (format != FPEMU_FMT_E5M2 && format != FPEMU_FMT_E4M3 && format != FPEMU_FMT_E3M4) return FPEMU_ERR_MODE;
   if (rounding < 0 || rounding >= FPEMU_RND_COUNT) return FPEMU_ERR_MODE;
-  if (!(scale <= 65504.0f)) return FPEMU_ERR_SCALE;
+  if (scale > 65504.0f) return FPEMU_ERR_SCALE;
   if (n > 0 && (wide == nullptr || codes == nullptr)) return FPEMU_ERR_ARG;
   if ((uintptr_t)wide % (uintptr_t)dtype_bytes(dtype)) return FPEMU_ERR_ALIGN;
   return FPEMU_OK;

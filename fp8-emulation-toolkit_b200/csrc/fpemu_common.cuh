@@ -54,9 +54,37 @@ __device__ __forceinline__ float effective_scale(float s, int dt) {
   return dt == FPEMU_DT_F16 ? __half2float(__float2half_rn(s)) : s;
 }
 
-// warp / block max of non-negative floats (integer max on the bit patterns is exact and NaN-free)
+// warp / block max of |x| values held as bit patterns: for non-negative floats the integer order of the encodings is
+// the numeric order, and every NaN encoding sorts above +Inf, so a NaN that reached the pattern stays the maximum
 __device__ __forceinline__ uint32_t warp_max_u32(uint32_t v) {
   return __reduce_max_sync(0xFFFFFFFFu, v);
+}
+
+// max(m, |x|) that returns NaN when either operand is NaN (what torch.max(abs(t)) does, mpemu/qutils.py:283) — one
+// FMNMX.NAN with the |.| source modifier
+__device__ __forceinline__ float absmax_nan(float m, float x) {
+  float r;
+  asm("max.NaN.f32 %0, %1, %2;" : "=f"(r) : "f"(m), "f"(fabsf(x)));
+  return r;
+}
+
+// The amax-derived scale of quantize_tensor (mpemu/qutils.py:283-285, :303-305, :328):
+//     scale = flt_max / vmax;  scale = 6.55e+04 if scale > 3.275e+04 else scale
+// `vmax` is a 0-dim tensor there, so `flt_max / vmax` is Tensor.__rtruediv__ = `vmax.reciprocal() * flt_max`
+// (torch/_tensor.py `__rdiv__`), evaluated in the tensor's dtype: two roundings, not one division.
+//   float32 tensors: fl32(fl32(1 / vmax) * flt_max);
+//   float16 tensors: the reciprocal is rounded to half, the product again, and the comparison with 3.275e4 runs in
+//                    half (3.275e4 -> 32752); the clamp value 6.55e4 reaches the kernel as a float and is rounded to
+//                    half there (65504) by effective_scale();
+//   bfloat16 tensors (not dispatched by the reference): float32 arithmetic on the widened values.
+__device__ __forceinline__ float scale_from_amax(float amax, float flt_max, bool clamp, int dt) {
+  if (dt == FPEMU_DT_F16) {
+    const float r = __half2float(__float2half_rn(__frcp_rn(amax)));
+    const float s = __half2float(__float2half_rn(__fmul_rn(r, flt_max)));
+    return (clamp && s > 32752.0f) ? 6.55e4f : s;
+  }
+  const float s = __fmul_rn(__frcp_rn(amax), flt_max);
+  return (clamp && s > 3.275e4f) ? 6.55e4f : s;
 }
 
 struct DeviceInfo { int sm_count; };

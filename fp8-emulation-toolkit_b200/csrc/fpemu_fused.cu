@@ -51,7 +51,7 @@ __global__ void __launch_bounds__(kThreads) fused_amax_cast_kernel(const CastArg
     }
   }
 #pragma unroll
-  for (int j = 0; j < R; ++j) m = fmaxf(m, vec_absmax<DT>(v[j]));
+  for (int j = 0; j < R; ++j) m = absmax_nan(m, vec_absmax<DT, true>(v[j]));
   // ragged tail (< one vector): CTA 0 keeps it in a zero-padded register vector as well
   const int tail = (int)(a.n - nvec * VE);
   Vec32 tv;
@@ -67,7 +67,7 @@ __global__ void __launch_bounds__(kThreads) fused_amax_cast_kernel(const CastArg
       const unsigned short* p = reinterpret_cast<const unsigned short*>(a.in) + e0;
       for (int i = 0; i < tail; ++i) tv.w[i >> 1] |= (uint32_t)p[i] << ((i & 1) * 16);
     }
-    m = fmaxf(m, vec_absmax<DT>(tv));
+    m = absmax_nan(m, vec_absmax<DT, true>(tv));
   }
   __shared__ uint32_t warp_bits[kThreads / 32];
   uint32_t bits = warp_max_u32(__float_as_uint(m));
@@ -89,8 +89,7 @@ __global__ void __launch_bounds__(kThreads) fused_amax_cast_kernel(const CastArg
 #pragma unroll
   for (int w = 1; w < kThreads / 32; ++w) all = max(all, warp_bits[w]);
   const float amax = __uint_as_float(all);
-  float s = __fdiv_rn(a.flt_max, amax);      // mpemu/qutils.py:283-285
-  if (s > 3.275e4f) s = 6.55e4f;
+  const float s = scale_from_amax(amax, a.flt_max, true, DT);   // mpemu/qutils.py:283-285
   if (blockIdx.x == 0 && threadIdx.x == 0) { d_work[0] = amax; d_work[1] = s; }
   ScaleCtx sc;
   sc.unscale32 = (a.flags & FPEMU_FLAG_UNSCALE_FP32) != 0;

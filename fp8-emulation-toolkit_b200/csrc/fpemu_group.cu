@@ -33,14 +33,21 @@ __global__ void __launch_bounds__(256) group_reg_kernel(const CastArgs a_, const
       for (int i = 0; i < 8; ++i) v[j].w[i] = 0u;
     }
   }
+  // rows follow torch.max(abs(row)) (a NaN makes the row's scale NaN, qutils.py:303), blocks follow absmax_block
+  // (NaN ignored, fpemu_kernels.cu:150-170); `rule` is uniform across the launch
+  if (rule == kRuleBlockPow2) {
 #pragma unroll
-  for (int j = 0; j < R; ++j) m = fmaxf(m, vec_absmax<DT>(v[j]));
+    for (int j = 0; j < R; ++j) m = fmaxf(m, vec_absmax<DT, false>(v[j]));
+  } else {
+#pragma unroll
+    for (int j = 0; j < R; ++j) m = absmax_nan(m, vec_absmax<DT, true>(v[j]));
+  }
   const float amax = group_absmax(m, lg);
   float s;
   if (rule == kRuleBlockPow2) {
     s = block_scale(amax, FMT, DT);
   } else {
-    const float s_host = scale_from_amax(amax, flt_max, rule == kRuleRowClamp);
+    const float s_host = scale_from_amax(amax, flt_max, rule == kRuleRowClamp, DT);
     if (d_scale_out != nullptr && live && tg == 0) d_scale_out[grp] = s_host;
     s = effective_scale(s_host, DT);
   }

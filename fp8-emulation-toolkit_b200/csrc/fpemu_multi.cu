@@ -165,9 +165,9 @@ __global__ void __launch_bounds__(kThreads) amax_multi_kernel(const void* table,
     }
   }
 #pragma unroll
-  for (int j = 0; j < kMtAmaxUnroll; ++j) m = fmaxf(m, vec_absmax<DT>(v[j]));
+  for (int j = 0; j < kMtAmaxUnroll; ++j) m = absmax_nan(m, vec_absmax<DT, true>(v[j]));
   if (local_cta == 0 && threadIdx.x < (int)(e.n - nvec * VE))
-    m = fmaxf(m, fabsf(load_elem(e.in, nvec * VE + threadIdx.x, DT)));
+    m = absmax_nan(m, load_elem(e.in, nvec * VE + threadIdx.x, DT));
   uint32_t bits = warp_max_u32(__float_as_uint(m));
   __shared__ uint32_t warp_bits[kThreads / 32];
   if ((threadIdx.x & 31) == 0) warp_bits[threadIdx.x >> 5] = bits;

@@ -47,7 +47,7 @@ constexpr int kScratchWords = kMaxParts + 64;                   // 65 792 bytes
 
 static __device__ __align__(256) uint32_t g_noalloc_scratch[kScratchWords];
 
-// |x| maximum of one CTA's 32 KiB slice -> parts[blockIdx.x].  NaN is ignored (fmaxf), as in fpemu_amax.
+// |x| maximum of one CTA's 32 KiB slice -> parts[blockIdx.x].  A NaN in the slice makes the slot NaN, as in fpemu_amax.
 __global__ void __launch_bounds__(kPartThreads) partial_amax_kernel(const void* in_, int64_t n, int dt, int aligned,
                                                                   uint32_t* parts) {
   const int esz = dtype_bytes(dt);
@@ -64,24 +64,24 @@ __global__ void __launch_bounds__(kPartThreads) partial_amax_kernel(const void* 
       const Vec32 v = ldg256(in + vi * 32);
       if (dt == FPEMU_DT_F32) {
 #pragma unroll
-        for (int i = 0; i < 8; ++i) m = fmaxf(m, fabsf(__uint_as_float(v.w[i])));
+        for (int i = 0; i < 8; ++i) m = absmax_nan(m, __uint_as_float(v.w[i]));
       } else if (dt == FPEMU_DT_F16) {
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
           const float2 f = unpack_f16x2(v.w[i]);
-          m = fmaxf(m, fmaxf(fabsf(f.x), fabsf(f.y)));
+          m = absmax_nan(absmax_nan(m, f.x), f.y);
         }
       } else {
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
           const float2 f = unpack_bf16x2(v.w[i]);
-          m = fmaxf(m, fmaxf(fabsf(f.x), fabsf(f.y)));
+          m = absmax_nan(absmax_nan(m, f.x), f.y);
         }
       }
     }
-    for (int64_t i = v1 * ve + threadIdx.x; i < e1; i += kPartThreads) m = fmaxf(m, fabsf(load_elem(in_, i, dt)));
+    for (int64_t i = v1 * ve + threadIdx.x; i < e1; i += kPartThreads) m = absmax_nan(m, load_elem(in_, i, dt));
   } else {
-    for (int64_t i = e0 + threadIdx.x; i < e1; i += kPartThreads) m = fmaxf(m, fabsf(load_elem(in_, i, dt)));
+    for (int64_t i = e0 + threadIdx.x; i < e1; i += kPartThreads) m = absmax_nan(m, load_elem(in_, i, dt));
   }
   uint32_t bits = warp_max_u32(__float_as_uint(m));             // non-negative floats order like their bits
   __shared__ uint32_t warp_bits[kPartThreads / 32];
@@ -95,7 +95,7 @@ __global__ void __launch_bounds__(kPartThreads) partial_amax_kernel(const void* 
 }
 
 // One CTA: maximum of parts[0 .. nparts) -> scratch[kSlotAmax]; clamp(flt_max / amax) -> scratch[kSlotScale].
-__global__ void __launch_bounds__(1024) finish_scale_kernel(uint32_t* scratch, int nparts, float flt_max) {
+__global__ void __launch_bounds__(1024) finish_scale_kernel(uint32_t* scratch, int nparts, float flt_max, int dt) {
   uint32_t bits = 0u;
   for (int i = threadIdx.x; i < nparts; i += 1024) bits = max(bits, scratch[i]);
   bits = warp_max_u32(bits);
@@ -106,8 +106,7 @@ __global__ void __launch_bounds__(1024) finish_scale_kernel(uint32_t* scratch, i
     bits = warp_max_u32(warp_bits[threadIdx.x]);
     if (threadIdx.x == 0) {
       const float amax = __uint_as_float(bits);
-      float s = __fdiv_rn(flt_max, amax);                       // `scale = flt_max / vmax`
-      if (s > 3.275e4f) s = 6.55e4f;                            // `6.55e+04 if scale > 3.275e+04`
+      const float s = scale_from_amax(amax, flt_max, true, dt);  // mpemu/qutils.py:283-285
       scratch[kSlotAmax] = bits;
       scratch[kSlotScale] = __float_as_uint(s);
     }
@@ -157,7 +156,7 @@ extern "C" int fpemu_cast_amax_scaled_noalloc(const void* in, void* out, int64_t
   partial_amax_kernel<<<nparts, kPartThreads, 0, stream>>>(in, n, dtype, aligned, scratch);
   cudaError_t err = cudaGetLastError();
   if (err != cudaSuccess) return (int)err;
-  finish_scale_kernel<<<1, 1024, 0, stream>>>(scratch, nparts, flt_max);
+  finish_scale_kernel<<<1, 1024, 0, stream>>>(scratch, nparts, flt_max, dtype);
   err = cudaGetLastError();
   if (err != cudaSuccess) return (int)err;
   return fpemu_cast(in, out, n, dtype, format, rounding, flags, 1.0f,

@@ -6,36 +6,33 @@
 namespace fpemu {
 
 // ------------------------------------------------------------------------------------------ amax
-// max |x| of one 32-byte vector as a non-negative float; NaN lanes are ignored (fmaxf / hmax2 semantics,
-// as the reference's absmax0, fpemu_kernels.cu:194-195).
-template <int DT>
+// max |x| of one 32-byte vector as a non-negative float.
+//   NANPROP = true : a NaN lane makes the result NaN, like torch.max(abs(t)) — the per-tensor / per-channel scale
+//                    derivations of mpemu/qutils.py:283, :303, :327 (the scale, and with it every output, is then NaN);
+//   NANPROP = false: NaN lanes are ignored (fmaxf semantics) — the reference's absmax_block of the blocked mode,
+//                    fpemu_kernels.cu:150-170.
+template <int DT, bool NANPROP>
 __device__ __forceinline__ float vec_absmax(const Vec32& v) {
   if (DT == FPEMU_DT_F32) {
     float m = 0.0f;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) m = fmaxf(m, fabsf(__uint_as_float(v.w[i])));
+    for (int i = 0; i < 8; ++i) m = NANPROP ? absmax_nan(m, __uint_as_float(v.w[i])) : fmaxf(m, fabsf(__uint_as_float(v.w[i])));
     return m;
   } else if (DT == FPEMU_DT_F16) {
     __half2 m = as_h2(0u);
 #pragma unroll
-    for (int i = 0; i < 8; ++i) m = __hmax2(m, as_h2(v.w[i] & kAbs2));
-    return fmaxf(__low2float(m), __high2float(m));
+    for (int i = 0; i < 8; ++i) m = NANPROP ? __hmax2_nan(m, as_h2(v.w[i] & kAbs2)) : __hmax2(m, as_h2(v.w[i] & kAbs2));
+    return NANPROP ? absmax_nan(__low2float(m), __high2float(m)) : fmaxf(__low2float(m), __high2float(m));
   } else {
     uint32_t z = 0u;
     __nv_bfloat162 m = *reinterpret_cast<__nv_bfloat162*>(&z);
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
       uint32_t a = v.w[i] & kAbs2;
-      m = __hmax2(m, *reinterpret_cast<__nv_bfloat162*>(&a));
+      m = NANPROP ? __hmax2_nan(m, *reinterpret_cast<__nv_bfloat162*>(&a)) : __hmax2(m, *reinterpret_cast<__nv_bfloat162*>(&a));
     }
-    return fmaxf(__low2float(m), __high2float(m));
+    return NANPROP ? absmax_nan(__low2float(m), __high2float(m)) : fmaxf(__low2float(m), __high2float(m));
   }
-}
-
-__device__ __forceinline__ float scale_from_amax(float amax, float flt_max, bool clamp) {
-  float s = __fdiv_rn(flt_max, amax);                       // `scale = flt_max / vmax`
-  if (clamp && s > 3.275e4f) s = 6.55e4f;                   // `scale = 6.55e+04 if scale > 3.275e+04`
-  return s;
 }
 
 // Power-of-two block scale from the block maximum (fpemu_kernels.cu:409-413, 577-581, 909-911, 998).

@@ -40,8 +40,8 @@ __global__ void __launch_bounds__(256) encode_rows_kernel(const CastArgs a_, con
     }
   }
 #pragma unroll
-  for (int j = 0; j < R; ++j) m = fmaxf(m, vec_absmax<DT>(v[j]));
-  const float s_host = scale_from_amax(group_absmax(m, lg), flt_max, clamp);
+  for (int j = 0; j < R; ++j) m = absmax_nan(m, vec_absmax<DT, true>(v[j]));
+  const float s_host = scale_from_amax(group_absmax(m, lg), flt_max, clamp, DT);
   if (live && tg == 0) d_row_scale[row] = s_host;
   ScaleCtx sc;
   sc.scale = effective_scale(s_host, DT);
@@ -72,9 +72,9 @@ __global__ void __launch_bounds__(256) encode_rows_generic_kernel(const CastArgs
   for (int64_t r = warp0; r < rows; r += nwarps) {
     const int64_t e0 = r * cols;
     float m = 0.0f;
-    for (int64_t i = lane; i < cols; i += 32) m = fmaxf(m, fabsf(load_elem(a.in, e0 + i, dt)));
+    for (int64_t i = lane; i < cols; i += 32) m = absmax_nan(m, load_elem(a.in, e0 + i, dt));
     m = __uint_as_float(warp_max_u32(__float_as_uint(m)));
-    const float s_host = scale_from_amax(m, flt_max, clamp);
+    const float s_host = scale_from_amax(m, flt_max, clamp, dt);
     if (lane == 0) d_row_scale[r] = s_host;
     const float s = effective_scale(s_host, dt);
     for (int64_t i = lane; i < cols; i += 32) {
@@ -335,7 +335,10 @@ extern "C" int fpemu_cast_rows_scaled(const void* in, void* out, int64_t rows, i
                                       int rounding, int flags, const float* d_row_scale, uint64_t seed,
                                       uint64_t elem_offset, void* stream_) {
   using namespace fpemu;
-  int st = validate_rows(in, out, d_row_scale, rows, cols, dtype, format, rounding);
+  // every format that takes a scale: the three 8-bit formats, and E4M3_IEEE / FP4 (which have no byte code, hence are
+  // not in validate_rows' list) — the reference's per-channel loop handles all of them (mpemu/qutils.py:289-311)
+  const bool extra = (format == FPEMU_FMT_E4M3_IEEE || format == FPEMU_FMT_FP4);
+  int st = validate_rows(in, out, d_row_scale, rows, cols, dtype, extra ? FPEMU_FMT_E4M3 : format, rounding);
   if (st != FPEMU_OK) return st;
   if ((uintptr_t)out % (uintptr_t)dtype_bytes(dtype)) return FPEMU_ERR_ALIGN;
   const int64_t n = rows * cols;
@@ -348,7 +351,9 @@ extern "C" int fpemu_cast_rows_scaled(const void* in, void* out, int64_t rows, i
   RowsScaledKernel k = nullptr;
   if (aligned && rng_ok && !(flags & FPEMU_FLAG_DAZ)) {
     k = format == FPEMU_FMT_E5M2 ? rs_rnd<FPEMU_FMT_E5M2>(rounding, dtype)
-      : format == FPEMU_FMT_E4M3 ? rs_rnd<FPEMU_FMT_E4M3>(rounding, dtype) : rs_rnd<FPEMU_FMT_E3M4>(rounding, dtype);
+      : format == FPEMU_FMT_E4M3 ? rs_rnd<FPEMU_FMT_E4M3>(rounding, dtype)
+      : format == FPEMU_FMT_E3M4 ? rs_rnd<FPEMU_FMT_E3M4>(rounding, dtype)
+      : format == FPEMU_FMT_E4M3_IEEE ? rs_rnd<FPEMU_FMT_E4M3_IEEE>(rounding, dtype) : nullptr;   // FP4: element-wise
   }
   if (k != nullptr) {
     const int u = dtype == FPEMU_DT_F32 ? UnrollFor<FPEMU_DT_F32>::value : UnrollFor<FPEMU_DT_F16>::value;

@@ -30,11 +30,11 @@ __global__ void __launch_bounds__(kAmaxThreads) amax_kernel(const void* in_, int
       }
     }
 #pragma unroll
-    for (int j = 0; j < kAmaxUnroll; ++j) m = fmaxf(m, vec_absmax<DT>(v[j]));
+    for (int j = 0; j < kAmaxUnroll; ++j) m = absmax_nan(m, vec_absmax<DT, true>(v[j]));
   }
   // ragged tail
   if (blockIdx.x == 0 && threadIdx.x < (int)(n - nvec * VE))
-    m = fmaxf(m, fabsf(load_elem(in_, nvec * VE + threadIdx.x, DT)));
+    m = absmax_nan(m, load_elem(in_, nvec * VE + threadIdx.x, DT));
   uint32_t bits = warp_max_u32(__float_as_uint(m));
   __shared__ uint32_t warp_bits[kAmaxThreads / 32];
   if ((threadIdx.x & 31) == 0) warp_bits[threadIdx.x >> 5] = bits;
@@ -53,14 +53,14 @@ __global__ void __launch_bounds__(256) amax_generic_kernel(const void* in, int64
   float m = 0.0f;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
-    m = fmaxf(m, fabsf(load_elem(in, i, dt)));
+    m = absmax_nan(m, load_elem(in, i, dt));
   uint32_t bits = warp_max_u32(__float_as_uint(m));
   if ((threadIdx.x & 31) == 0 && bits != 0u) atomicMax(reinterpret_cast<unsigned int*>(d_amax), bits);
 }
 
-__global__ void scale_from_amax_kernel(const float* d_amax, int count, float flt_max, float* d_scale) {
+__global__ void scale_from_amax_kernel(const float* d_amax, int count, float flt_max, int dt, float* d_scale) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < count) d_scale[i] = scale_from_amax(d_amax[i], flt_max, true);
+  if (i < count) d_scale[i] = scale_from_amax(d_amax[i], flt_max, true, dt);
 }
 
 // ------------------------------------------------------------------------------------------ blocked
@@ -86,7 +86,7 @@ __global__ void __launch_bounds__(kThreads) blocked_vec_kernel(const CastArgs a_
 #pragma unroll
       for (int i = 0; i < 8; ++i) v.w[i] = 0u;
     }
-    uint32_t mb = __float_as_uint(vec_absmax<DT>(v));
+    uint32_t mb = __float_as_uint(vec_absmax<DT, false>(v));   // NaN ignored: absmax_block, :150-170
     for (int d = 1; d < vpb; d <<= 1) mb = max(mb, __shfl_xor_sync(0xFFFFFFFFu, mb, d));
     const float s = block_scale(__uint_as_float(mb), FMT, DT);
     sc.scale = s;
@@ -115,6 +115,29 @@ __global__ void __launch_bounds__(256) blocked_generic_kernel(const CastArgs a_,
     const float s = block_scale(m, a.fmt, dt);
     const float rs = __frcp_rn(s);
     for (int64_t i = lane; i < block_size; i += 32) {
+      const float x = load_elem(a.in, e0 + i, dt);
+      uint32_t rb = 0u;
+      if (a.rnd == FPEMU_RND_STOCHASTIC) rb = rand_bits_one(a.seed_lo, a.seed_hi, a.elem_offset + (uint64_t)(e0 + i), wide);
+      store_elem(a.out, e0 + i, dt, cast_one(x, a.fmt, a.rnd, a.flags, true, s, rs, dt == FPEMU_DT_F16, rb));
+    }
+  }
+}
+
+// Blocks shorter than a warp: one THREAD per block (a warp per block would leave 31 of 32 lanes idle).  The reference's
+// embedding call binds block_size = 1 (mpemu/hybrid_emu.py:119 passes the row length in the `blocknorm` slot), i.e. every
+// element gets its own power-of-two scale: that case is fully coalesced here.
+__global__ void __launch_bounds__(256) blocked_small_kernel(const CastArgs a_, const int block_size, const int dt) {
+  const CastArgs a = with_device_seed(a_);
+  const int64_t nblocks = a.n / block_size;
+  const bool wide = (a.fmt == FPEMU_FMT_BF16 || a.fmt == FPEMU_FMT_FP16);
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; b < nblocks; b += stride) {
+    const int64_t e0 = b * block_size;
+    float m = 0.0f;
+    for (int i = 0; i < block_size; ++i) m = fmaxf(m, fabsf(load_elem(a.in, e0 + i, dt)));
+    const float s = block_scale(m, a.fmt, dt);
+    const float rs = __frcp_rn(s);
+    for (int i = 0; i < block_size; ++i) {
       const float x = load_elem(a.in, e0 + i, dt);
       uint32_t rb = 0u;
       if (a.rnd == FPEMU_RND_STOCHASTIC) rb = rand_bits_one(a.seed_lo, a.seed_hi, a.elem_offset + (uint64_t)(e0 + i), wide);
@@ -171,10 +194,10 @@ __global__ void __launch_bounds__(kThreads) rowwise_vec_kernel(const CastArgs a_
     float m = 0.0f;
     for (int64_t vi = lane; vi < vpr; vi += 32) {
       const Vec32 v = *reinterpret_cast<const Vec32*>(in + vi * 32);   // default caching: pass 2 hits L1
-      m = fmaxf(m, vec_absmax<DT>(v));
+      m = absmax_nan(m, vec_absmax<DT, true>(v));
     }
     m = __uint_as_float(warp_max_u32(__float_as_uint(m)));
-    const float s_host = scale_from_amax(m, flt_max, clamp);
+    const float s_host = scale_from_amax(m, flt_max, clamp, DT);
     if (d_row_scale != nullptr && lane == 0) d_row_scale[r] = s_host;
     const float s = effective_scale(s_host, DT);
     sc.scale = s;
@@ -198,9 +221,9 @@ __global__ void __launch_bounds__(256) rowwise_generic_kernel(const CastArgs a_,
   for (int64_t r = warp0; r < rows; r += nwarps) {
     const int64_t e0 = r * cols;
     float m = 0.0f;
-    for (int64_t i = lane; i < cols; i += 32) m = fmaxf(m, fabsf(load_elem(a.in, e0 + i, dt)));
+    for (int64_t i = lane; i < cols; i += 32) m = absmax_nan(m, load_elem(a.in, e0 + i, dt));
     m = __uint_as_float(warp_max_u32(__float_as_uint(m)));
-    const float s_host = scale_from_amax(m, flt_max, clamp);
+    const float s_host = scale_from_amax(m, flt_max, clamp, dt);
     if (d_row_scale != nullptr && lane == 0) d_row_scale[r] = s_host;
     const float s = effective_scale(s_host, dt);
     const float rs = __frcp_rn(s);
@@ -291,11 +314,18 @@ extern "C" int fpemu_amax(const void* in, int64_t n, int dtype, float* d_amax, v
   return (int)cudaGetLastError();
 }
 
-extern "C" int fpemu_scale_from_amax(const float* d_amax, int count, float flt_max, float* d_scale, void* stream_) {
+extern "C" int fpemu_scale_from_amax_dtype(const float* d_amax, int count, float flt_max, int dtype, float* d_scale,
+                                           void* stream_) {
   if (count < 0 || (count > 0 && (d_amax == nullptr || d_scale == nullptr))) return FPEMU_ERR_ARG;
+  if (dtype < 0 || dtype >= FPEMU_DT_COUNT) return FPEMU_ERR_DTYPE;
   if (count == 0) return FPEMU_OK;
-  scale_from_amax_kernel<<<(count + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream_)>>>(d_amax, count, flt_max, d_scale);
+  scale_from_amax_kernel<<<(count + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream_)>>>(d_amax, count, flt_max, dtype,
+                                                                                             d_scale);
   return (int)cudaGetLastError();
+}
+
+extern "C" int fpemu_scale_from_amax(const float* d_amax, int count, float flt_max, float* d_scale, void* stream_) {
+  return fpemu_scale_from_amax_dtype(d_amax, count, flt_max, FPEMU_DT_F32, d_scale, stream_);
 }
 
 extern "C" int fpemu_cast_blocked(const void* in, void* out, int64_t n, int64_t block_size, int dtype, int format,
@@ -325,6 +355,10 @@ extern "C" int fpemu_cast_blocked(const void* in, void* out, int64_t n, int64_t 
     const int64_t want = (n / ve + kThreads - 1) / kThreads;
     if (want > 0x7FFFFFFFLL) return FPEMU_ERR_TOO_LARGE;
     k<<<(unsigned)want, kThreads, 0, stream>>>(a, (int)vpb);
+  } else if (block_size < 32) {
+    int64_t want = (n / block_size + 255) / 256;             // one thread per block
+    const int64_t cap = (int64_t)sms * 16;
+    blocked_small_kernel<<<(int)(want < cap ? want : cap), 256, 0, stream>>>(a, (int)block_size, dtype);
   } else {
     int64_t want = (n / block_size + 7) / 8;                 // 8 warps per CTA, one warp per block
     const int64_t cap = (int64_t)sms * 8;

@@ -26,6 +26,7 @@ SIGNATURES = {
     "fpemu_cast_blocked": (_i32, [_vp, _vp, _i64, _i64, _i32, _i32, _i32, _i32, _u64, _u64, _vp]),
     "fpemu_amax": (_i32, [_vp, _i64, _i32, _vp, _vp]),
     "fpemu_scale_from_amax": (_i32, [_vp, _i32, _f32, _vp, _vp]),
+    "fpemu_scale_from_amax_dtype": (_i32, [_vp, _i32, _f32, _i32, _vp, _vp]),
     "fpemu_cast_amax_scaled": (_i32, [_vp, _vp, _i64, _i32, _i32, _i32, _i32, _f32, _vp, _u64, _u64, _vp]),
     "fpemu_cast_rowwise": (_i32, [_vp, _vp, _i64, _i64, _i32, _i32, _i32, _i32, _f32, _vp, _u64, _u64, _vp]),
     "fpemu_multi_table_bytes": (_i64, [_i32]),

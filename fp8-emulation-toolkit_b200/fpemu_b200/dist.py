@@ -64,7 +64,7 @@ def sharded_amax_scaled_cast(slabs, mode, row_offsets=None, cols=None, outs=None
     row_offsets = row_offsets or [0] * n
     cols = cols or [(x.shape[-1] if x.dim() > 1 else 1) for x in slabs]
     amax_vec = global_amax(slabs, group=group, kernels=kernels)
-    scales = kernels.scale_from_amax(amax_vec, flt_max)
+    scales = kernels.scale_from_amax(amax_vec, flt_max, dtype=slabs[0].dtype)
     results = []
     for t, x in enumerate(slabs):
         out = None if outs is None else outs[t]
@@ -83,7 +83,7 @@ def sharded_amax_scaled_encode(slabs, mode, row_offsets=None, cols=None, outs=No
     n = len(slabs)
     row_offsets = row_offsets or [0] * n
     cols = cols or [(x.shape[-1] if x.dim() > 1 else 1) for x in slabs]
-    scales = kernels.scale_from_amax(global_amax(slabs, group=group, kernels=kernels), flt_max)
+    scales = kernels.scale_from_amax(global_amax(slabs, group=group, kernels=kernels), flt_max, dtype=slabs[0].dtype)
     codes = [kernels.encode(x, mode, out=None if outs is None else outs[t], d_scale=scales[t:t + 1], seed=seed + t,
                             elem_offset=row_offsets[t] * cols[t], expect_normals=True) for t, x in enumerate(slabs)]
     return codes, scales

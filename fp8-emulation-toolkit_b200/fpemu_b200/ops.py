@@ -76,6 +76,13 @@ def _check_tensor(t, name="input"):
         raise RuntimeError("%s must be contiguous" % name)              # CHECK_CONTIGUOUS, :24
 
 
+def _check_out(out, x, n):
+    """A caller-supplied output: CUDA, contiguous, same device and dtype as the input, room for n elements."""
+    _check_tensor(out, "out")
+    if out.dtype != x.dtype or out.device != x.device or out.numel() < n:
+        raise ValueError("fpemu: out must match the input's dtype and device and hold at least %d elements" % n)
+
+
 def _stream(t):
     """cudaStream_t (as int) of torch's current stream on t's device."""
     if _raw_stream is not None:
@@ -208,9 +215,13 @@ def cast_blocked(x, mode, block_size, out=None, seed=None, elem_offset=0, n=None
     fmt, rnd, flags = L.parse_mode(mode)
     if unscale_fp32:
         flags |= L.FLAG_UNSCALE_FP32
+    n = x.numel() if n is None else int(n)
+    if n > x.numel():
+        raise ValueError("fpemu: size larger than the tensor")
     if out is None:
         out = torch.empty_like(x)
-    n = x.numel() if n is None else int(n)
+    else:
+        _check_out(out, x, n)
     if rnd == L.RND_STOCHASTIC and seed is None:
         seed = next_seed()
     if int(block_size) == n and n > (1 << 16) and fmt in (L.FMT_E5M2, L.FMT_E4M3, L.FMT_E3M4, L.FMT_E4M3_IEEE) \
@@ -249,13 +260,15 @@ def amax(x, out=None, n=None):
     return out
 
 
-def scale_from_amax(d_amax, flt_max, out=None):
-    """clamp(flt_max / amax) on the device (qutils.py:283-285), elementwise over a float32 CUDA vector."""
+def scale_from_amax(d_amax, flt_max, out=None, dtype=torch.float32):
+    """The scale quantize_tensor derives from a maximum (`flt_max / vmax` + clamp, qutils.py:283-285), on the device,
+    elementwise over a float32 CUDA vector.  `dtype`: element type of the tensors the maxima came from — torch
+    evaluates `flt_max / vmax` as `vmax.reciprocal() * flt_max` in that type (two roundings in half for float16)."""
     if out is None:
         out = torch.empty_like(d_amax)
     with _on_device(d_amax):
-        st = L.lib().fpemu_scale_from_amax(d_amax.data_ptr(), d_amax.numel(), float(flt_max), out.data_ptr(),
-                                           _stream(d_amax))
+        st = L.lib().fpemu_scale_from_amax_dtype(d_amax.data_ptr(), d_amax.numel(), float(flt_max), _DT[dtype],
+                                                 out.data_ptr(), _stream(d_amax))
     L.check(st, "fpemu_scale_from_amax")
     return out
 
@@ -297,7 +310,7 @@ def cast_amax_scaled(x, mode, out=None, flt_max=None, seed=None, elem_offset=0, 
     if flt_max is None:
         flt_max = FLT_MAX[fmt]
     if d_amax is not None:
-        d_scale = scale_from_amax(d_amax, flt_max)
+        d_scale = scale_from_amax(d_amax, flt_max, dtype=x.dtype)
         y = cast(x, mode, out=out, d_scale=d_scale, seed=seed, elem_offset=elem_offset, unscale_fp32=unscale_fp32)
         return (y, d_scale) if return_scale else y
     _check_tensor(x)
@@ -362,8 +375,12 @@ def cast_rowwise(x2d, mode, out=None, flt_max=None, clamp=True, seed=None, elem_
     if rows is None:
         rows = x2d.shape[0] if x2d.dim() > 0 else 1
         cols = x2d.numel() // max(rows, 1)
+    if rows * cols > x2d.numel():
+        raise ValueError("fpemu: rows * cols larger than the tensor")
     if out is None:
         out = torch.empty_like(x2d)
+    else:
+        _check_out(out, x2d, rows * cols)
     scales = torch.empty(rows, dtype=torch.float32, device=x2d.device) if return_scales else None
     if rnd == L.RND_STOCHASTIC and seed is None:
         seed = next_seed()
@@ -536,7 +553,7 @@ class MultiTensorPlan(object):
         vec = self.amax()
         if reduce_fn is not None:
             reduce_fn(vec)
-        scales = scale_from_amax(vec, FLT_MAX[fmt] if flt_max is None else flt_max)
+        scales = scale_from_amax(vec, FLT_MAX[fmt] if flt_max is None else flt_max, dtype=self.dtype)
         return self.encode(mode, d_scales=scales, seed=seed, expect_normals=True), scales   # scaled to the maximum
 
     def cast(self, mode, d_scales=None, seed=None, unscale_fp32=False):
@@ -568,7 +585,7 @@ class MultiTensorPlan(object):
         vec = self.amax()
         if reduce_fn is not None:
             reduce_fn(vec)
-        scales = scale_from_amax(vec, flt_max)
+        scales = scale_from_amax(vec, flt_max, dtype=self.dtype)
         return self.cast(mode, d_scales=scales, seed=seed, unscale_fp32=unscale_fp32), scales
 
 

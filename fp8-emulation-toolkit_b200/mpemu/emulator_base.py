@@ -209,25 +209,34 @@ class EmulatorBase(object):
                 self._warned_master = True
             return
         from .pytquant import fpemu_cuda
+        masters = [p for p in masters]
+        if not self.use_fp16_master:
+            # update_e5m2_master_params (hybrid_emu.py:178-190, e5m2_emu.py same): EVERY master parameter gets
+            # FLOAT16_STOCHASTIC and then E5M2_STOCHASTIC; embeddings are not special here.  Two multi-tensor launches.
+            plain = [p.data for p in masters if p.is_cuda]
+            self._cast_list_in_place(plain, "FLOAT16_STOCHASTIC")
+            self._cast_list_in_place(plain, "E5M2_STOCHASTIC")
+            return
+        # update_fp16_master_params (hybrid_emu.py:110-139): FLOAT16_STOCHASTIC for every master (one multi-tensor
+        # launch), then the embedding tables once more with the selected fp8 format
         emb_mode = ("E5M2_STOCHASTIC" if self.use_e5m2_emb else "E4M3_STOCHASTIC" if self.use_e4m3_emb
                     else "E3M4_STOCHASTIC" if self.use_e3m4_emb else None)
-        plain = []
+        plain, embs = [], []
         for param, (name, _) in zip(masters, self.model.named_parameters()):
             if not param.is_cuda:
                 continue
-            if not (emb_mode is not None and "embeddings" in name) and (self.use_fp16_master or self.use_e5m2_master):
-                plain.append(param.data)
-                continue
+            plain.append(param.data)
             if emb_mode is not None and "embeddings" in name:
-                param.data = fpemu_cuda.FPEmuOp.apply(param.data, "FLOAT16_STOCHASTIC", True)
-                if self.emb_norm:
-                    # the reference call passes (emb_norm, row_length) in the (scale, blocknorm) slots
-                    # (hybrid_emu.py:119); the intent — one block per embedding row — is what runs here
-                    param.data = fpemu_cuda.FPEmuOp.apply(param.data, emb_mode, True, 1.0, True, param.size()[1])
-                else:
-                    param.data = fpemu_cuda.FPEmuOp.apply(param.data, emb_mode, True)
-        if plain:
-            self._cast_list_in_place(plain, "FLOAT16_STOCHASTIC" if self.use_fp16_master else "E5M2_STOCHASTIC")
+                embs.append(param)
+        self._cast_list_in_place(plain, "FLOAT16_STOCHASTIC")
+        if embs and not self.emb_norm:
+            self._cast_list_in_place([p.data for p in embs], emb_mode)
+        for param in (embs if self.emb_norm else []):
+            # The reference passes (emb_norm, row_length) in the (scale, blocknorm) slots of FPEmuOp.apply
+            # (hybrid_emu.py:119): scale = float(emb_norm), blocknorm = truthy, blocksize stays 1 — so what EXECUTES
+            # there is a blocked cast with one block per ELEMENT (each value scaled by its own power of two), not one
+            # block per embedding row.  The same call is made here, binding for binding.
+            param.data = fpemu_cuda.FPEmuOp.apply(param.data, emb_mode, True, self.emb_norm, param.size()[1])
 
     def optimizer_step(self, optimizer):
         optimizer.step()

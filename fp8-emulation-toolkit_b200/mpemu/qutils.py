@@ -186,8 +186,10 @@ def _mean_scale(mean, flt_min, floor):
     The reference divides a Python float by a float32 tensor, i.e. in float32 — so does this."""
     import numpy as np
     mean = abs(float(mean))
-    mean = mean if mean > floor else flt_min
-    scale = float(np.float32(flt_min) / np.float32(mean)) if mean > 0.0 else 1.0
+    if not mean > floor:
+        return 1.0                       # `mean` becomes the Python float flt_min there: flt_min / flt_min
+    # `flt_min / abs(mean)` with `mean` a 0-dim tensor is `mean.reciprocal() * flt_min` (torch/_tensor.py __rdiv__)
+    scale = float(np.float32(np.float32(1.0) / np.float32(mean)) * np.float32(flt_min))
     return 1.0 if scale < 1.0 else scale
 
 
@@ -280,7 +282,7 @@ def quantize_tensor(tensor, qtconfig, qtparams, inplace=False):
             # numbers from ONE torch.mode over dim 1 (checked equal to the per-channel calls, ties included), the
             # scale expression of :298-301 on the device, and one row-wise launch with those scales: no .item().
             flt_min = qtconfig.get_flt_min()
-            if takes_scale and _supported_dtype(tensor) and channels > 0 and cols > 0:
+            if takes_scale and _supported_dtype(tensor) and channels > 0 and cols > 0:     # incl. E4M3_IEEE, FP4
                 src = tensor.detach()
                 src = src if src.is_contiguous() else src.contiguous()
                 m = torch.abs(torch.mode(src.reshape(channels, cols), dim=1).values).float()
@@ -321,7 +323,8 @@ def quantize_tensor(tensor, qtconfig, qtparams, inplace=False):
                     m = abs(torch.mode(torch.flatten(sub)).values.item())
                     scale = _mean_scale(m, qtconfig.get_flt_min(), 1e-6)
                 else:
-                    scale = flt_max / torch.max(torch.abs(sub)).item()
+                    # a 0-dim tensor like the reference's (`reciprocal * flt_max`); an all-zero group gives inf
+                    scale = (flt_max / torch.max(torch.abs(sub))).float().reshape(1)
                 sub.copy_(fpemu_device_fn(sub.contiguous(), mode, inplace=False, scale=scale))
         return out
 

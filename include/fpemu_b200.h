@@ -112,7 +112,9 @@ FPEMU_API int fpemu_parse_mode(const char* mode, int* format, int* rounding, int
 /* Elementwise quantize-dequantize cast of n elements: out[i] = QDQ(in[i]).  in == out is allowed
  * (in-place).  Replaces the kernel launches of fpemu_cuda_forward (fpemu_kernels.cu:1028-1381) for
  * block_norm == false.
- *   scale    host scalar applied before rounding; the result is multiplied by 1/scale.
+ *   scale    host scalar applied before rounding; the result is multiplied by 1/scale.  Larger than 65504:
+ *            FPEMU_ERR_SCALE (reference: exit(1), :1037-1041); a NaN passes that test there and here, and
+ *            turns every output into NaN.
  *   d_scale  optional DEVICE pointer to one float; when non-NULL it overrides `scale` (no host sync;
  *            fed by fpemu_scale_from_amax).
  *   seed, elem_offset  stochastic rounding uses Philox4x32-10 keyed by seed with the counter derived
@@ -132,17 +134,26 @@ FPEMU_API int fpemu_cast_blocked(const void* in, void* out, int64_t n, int64_t b
                        int rounding, int flags, uint64_t seed, uint64_t elem_offset, void* stream);
 
 /* Single-pass absolute maximum of n elements, max-accumulated into *d_amax (device float the caller
- * initialised, normally to 0; NaN inputs are ignored like torch.max on |x| never is — see DESIGN.md).
- * Replaces `torch.max(torch.abs(tensor.flatten()))` of mpemu/qutils.py:282. */
+ * initialised, normally to 0).  A NaN element makes the result NaN, exactly as
+ * `torch.max(torch.abs(tensor.flatten()))` of mpemu/qutils.py:283 does (the scale derived from it and every
+ * value cast with that scale are then NaN too — DESIGN.md §2 "NaN in the maximum"); the maximum is kept as a bit
+ * pattern, where every NaN sorts above +Inf, so the accumulation stays one integer atomicMax. */
 FPEMU_API int fpemu_amax(const void* in, int64_t n, int dtype, float* d_amax, void* stream);
 
-/* d_scale[i] = clamp(flt_max / d_amax[i]) for i < count, with the reference's clamp
- * `scale = 6.55e4 if scale > 3.275e4` (mpemu/qutils.py:283-285).  Device-side, no host sync. */
+/* d_scale[i] = the scale quantize_tensor derives from the maximum d_amax[i], for i < count:
+ *     scale = flt_max / vmax;  scale = 6.55e4 if scale > 3.275e4 else scale        (mpemu/qutils.py:283-285)
+ * `vmax` is a 0-dim tensor there, so torch evaluates the division as `vmax.reciprocal() * flt_max` in the tensor's
+ * element type: fl32(fl32(1 / vmax) * flt_max) for float32 (and bfloat16, which the reference does not dispatch);
+ * reciprocal, product and comparison each rounded to / done in half for float16.  `dtype` names that element type;
+ * fpemu_scale_from_amax is the float32 form.  Device-side, no host sync.  Every entry point below that derives a
+ * scale from a maximum (amax-scaled, row-wise, fused, no-alloc, multi) uses the same rule for its tensor's type. */
 FPEMU_API int fpemu_scale_from_amax(const float* d_amax, int count, float flt_max, float* d_scale, void* stream);
+FPEMU_API int fpemu_scale_from_amax_dtype(const float* d_amax, int count, float flt_max, int dtype, float* d_scale,
+                                          void* stream);
 
 /* Per-tensor amax-scaled cast in one call (the per-tensor `max` branch of quantize_tensor, mpemu/qutils.py:274-287):
- * clears d_work[0..1], reduces max|x| into d_work[0] and casts with scale = clamp(flt_max / amax), which the cast
- * kernel derives itself and stores in d_work[1].  d_work: two device floats owned by the caller (scratch; calls that
+ * clears d_work[0..1], reduces max|x| into d_work[0] and casts with the scale fpemu_scale_from_amax_dtype defines,
+ * which the cast kernel derives itself and stores in d_work[1].  d_work: two device floats owned by the caller (scratch; calls that
  * overlap on the GPU need separate d_work).  Three enqueues on `stream`, no host sync. */
 FPEMU_API int fpemu_cast_amax_scaled(const void* in, void* out, int64_t n, int dtype, int format, int rounding,
                                      int flags, float flt_max, float* d_work, uint64_t seed, uint64_t elem_offset,
@@ -206,7 +217,9 @@ FPEMU_API int fpemu_decode_rowwise(const void* codes, void* out, int64_t rows, i
 /* Row-wise cast with caller-supplied scales: row r is cast with scale d_row_scale[r] (read on the device, no host sync).
  * For per-channel scales that are not derived from the row maximum — the reference's per-channel `mean` scaling takes
  * torch.mode of each channel and calls the op once per channel (mpemu/qutils.py:289-311 with :294-301); this is that
- * loop as one launch.  Vector path: buffers 32-byte aligned, cols a multiple of 8 (float32) / 16 (16-bit). */
+ * loop as one launch.  Formats: every one that takes a scale (E5M2, E4M3, E3M4, E4M3_IEEE, FP4; BFLOAT16 / FLOAT16
+ * return FPEMU_ERR_MODE).  Vector path: buffers 32-byte aligned, cols a multiple of 8 (float32) / 16 (16-bit); FP4
+ * always runs the element-wise kernel. */
 FPEMU_API int fpemu_cast_rows_scaled(const void* in, void* out, int64_t rows, int64_t cols, int dtype, int format,
                            int rounding, int flags, const float* d_row_scale, uint64_t seed, uint64_t elem_offset,
                            void* stream);

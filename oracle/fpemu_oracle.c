@@ -10,8 +10,8 @@
  *
  * PARITY PIN: the restatement is checked bit-for-bit against outputs of the reference's own CPU
  * implementation (scalar build of cpp/fpemu_impl.cpp, see oracle/build_ref.py) on the exhaustive set
- * of 65 536 fp16 patterns, the reference's 64-value fixture (test.py:120-135) and wide-range random
- * fp32 inputs — fixtures in tests/golden/, generator tests/golden/make_golden.py — and, on the GPU
+ * of 65 536 fp16 patterns, the reference's 64-value fixture (test.py:120-135; tests/golden/fixture64.npz) and
+ * wide-range random fp32 inputs — fixtures in tests/golden/, generator tests/golden/make_golden.py — and, on the GPU
  * box, against the reference CUDA kernels compiled unmodified for sm_100a (oracle/_ref/fpemu_cuda_ref.so).
  * The reference's own tests hold no golden vectors (test.py only prints).
  *
@@ -567,16 +567,37 @@ int fpemu_oracle_cast_blocked(const void* in, void* out, int64_t n, int64_t bloc
   return FPEMU_OK;
 }
 
-/* max |x| over n elements, NaN ignored (fmaxf semantics of absmax0, cuda/fpemu_kernels.cu:194-195). */
+/* max |x| over n elements the way `torch.max(torch.abs(t.flatten()))` computes it (mpemu/qutils.py:283, :303, :327):
+ * a NaN anywhere makes the result NaN (torch.max propagates NaN).  The blocked mode's own maximum
+ * (absmax_block, cuda/fpemu_kernels.cu:150-170: fmaxf, NaN ignored) lives in fpemu_oracle_cast_blocked above. */
 float fpemu_oracle_amax(const void* in, int64_t n, int dtype) {
   float m = 0.0f;
-  for (int64_t i = 0; i < n; ++i) m = fmaxf(m, fabsf(load_elem(in, i, dtype)));
+  for (int64_t i = 0; i < n; ++i) {
+    const float a = fabsf(load_elem(in, i, dtype));
+    if (a != a) return a;
+    m = fmaxf(m, a);
+  }
   return m;
 }
 
-/* scale = flt_max / amax with the clamp of mpemu/qutils.py:283-285. */
+/* The scale quantize_tensor derives from the maximum (mpemu/qutils.py:283-285; per channel :303-305):
+ *     scale = flt_max / vmax;  scale = 6.55e+04 if scale > 3.275e+04 else scale
+ * `vmax` is a 0-dim tensor, so the division is Tensor.__rtruediv__, which torch implements as
+ * `vmax.reciprocal() * flt_max` (torch/_tensor.py, `__rdiv__`): the reciprocal is rounded to the tensor's dtype, the
+ * product again.  For a half tensor both roundings and the `>` comparison happen in half (3.275e4 is 32752 there);
+ * the clamp value travels as the Python float 6.55e4 and is rounded to half (65504) when the kernel takes its
+ * `scalar_t scale` argument (kernel_scale()).  bfloat16 is not dispatched by the reference: float arithmetic on the
+ * widened values.  `clamp` = 0 restates the fine-grained branch, which has no second line (:327-328). */
+float fpemu_oracle_scale_from_amax_dtype(float amax, float flt_max, int dtype, int clamp) {
+  if (dtype == FPEMU_DT_F16) {
+    const float r = fpemu_oracle_half2float(fpemu_oracle_float2half((float)(1.0 / (double)amax)));
+    const float s = fpemu_oracle_half2float(fpemu_oracle_float2half(mul_f32(r, flt_max)));
+    return (clamp && s > 32752.0f) ? 6.55e4f : s;
+  }
+  const float s = mul_f32((float)(1.0 / (double)amax), flt_max);
+  return (clamp && s > 3.275e4f) ? 6.55e4f : s;
+}
+
 float fpemu_oracle_scale_from_amax(float amax, float flt_max) {
-  float s = flt_max / amax;
-  if (s > 3.275e4f) s = 6.55e4f;
-  return s;
+  return fpemu_oracle_scale_from_amax_dtype(amax, flt_max, FPEMU_DT_F32, 1);
 }

@@ -49,6 +49,8 @@ def lib():
         L.fpemu_oracle_amax.restype = f32
         L.fpemu_oracle_scale_from_amax.argtypes = [f32, f32]
         L.fpemu_oracle_scale_from_amax.restype = f32
+        L.fpemu_oracle_scale_from_amax_dtype.argtypes = [f32, f32, i32, i32]
+        L.fpemu_oracle_scale_from_amax_dtype.restype = f32
         L.fpemu_oracle_rand_bits.argtypes = [u64, u64, i64, i32, vp]
         L.fpemu_oracle_rand_bits.restype = None
         L.fpemu_oracle_philox4x32_10.argtypes = [u64, u64, vp]
@@ -181,17 +183,21 @@ def amax(x):
     return float(lib().fpemu_oracle_amax(x.ctypes.data, x.size, _np_dtype_code(x)))
 
 
-def scale_from_amax(a, flt_max):
-    return float(lib().fpemu_oracle_scale_from_amax(float(a), float(flt_max)))
+def scale_from_amax(a, flt_max, like=None, clamp=True):
+    """`flt_max / vmax` + clamp of mpemu/qutils.py:283-285 (torch evaluates it as reciprocal * flt_max in the tensor's
+    dtype).  `like`: the tensor (numpy array) whose dtype the arithmetic follows; default float32."""
+    dt = DT["f32"] if like is None else _np_dtype_code(like)
+    return float(lib().fpemu_oracle_scale_from_amax_dtype(float(a), float(flt_max), dt, 1 if clamp else 0))
 
 
-def cast_rowwise(x2d, mode, flt_max, unscale_fp32=False):
-    """Per-channel amax-scaled cast, the loop of mpemu/qutils.py:289-311 restated over the oracle."""
+def cast_rowwise(x2d, mode, flt_max, unscale_fp32=False, clamp=True):
+    """Per-channel amax-scaled cast, the loop of mpemu/qutils.py:289-311 restated over the oracle (clamp=False: the
+    fine-grained branch :313-337 over its groups)."""
     x2d = np.ascontiguousarray(x2d)
     out = np.empty_like(x2d)
     scales = np.empty(x2d.shape[0], dtype=np.float32)
     for r in range(x2d.shape[0]):
-        s = scale_from_amax(amax(x2d[r]), flt_max)
+        s = scale_from_amax(amax(x2d[r]), flt_max, like=x2d, clamp=clamp)
         scales[r] = s
         out[r] = cast(x2d[r], mode, scale=s, unscale_fp32=unscale_fp32)
     return out, scales
@@ -203,7 +209,7 @@ def encode_rowwise(x2d, mode, flt_max, seed=0, elem_offset=0):
     codes = np.empty(x2d.shape, dtype=np.uint8)
     scales = np.empty(x2d.shape[0], dtype=np.float32)
     for r in range(x2d.shape[0]):
-        s = scale_from_amax(amax(x2d[r]), flt_max)
+        s = scale_from_amax(amax(x2d[r]), flt_max, like=x2d)
         scales[r] = s
         codes[r] = encode(x2d[r], mode, scale=s, seed=seed, elem_offset=elem_offset + r * x2d.shape[1])
     return codes, scales

@@ -19,6 +19,8 @@ Files:
   blocked.npz         blocked (block_norm) outputs for block sizes {32, 64, 1024}
   stochastic.npz      round-up counts of repeated draws for a few probe values (distribution pin)
   modules.npz         per-tensor / per-channel quantize_tensor outputs of the reference qutils (CPU)
+  fixture64.npz       the reference's own 64-value test vector (mpemu/pytquant/test.py:120-135) x modes x scales {1, 3.7}
+                      (`python tests/golden/make_golden.py fixture64` regenerates only this file)
 """
 import os
 import sys
@@ -58,6 +60,39 @@ def wide_inputs(n=4096, seed=1234):
     return x
 
 
+def reference_fixture64():
+    """The input vector of the reference's only test script (mpemu/pytquant/test.py:120-135): 64 float32 values chosen
+    around the formats' maxima, saturation points and flush thresholds.  That script prints input next to output and
+    asserts nothing, so the expected outputs are produced here by running the reference op on it."""
+    return np.array([57344.00, -61440.0, 65504.0, -500.0, 448.0, -480.0, 30.0, -31.0,
+                     26.0, 15.0, -7.6505613e-00, 5.9832452e-00, 1.5625032e-02, 3.1725775e-02, 4.3268750e-02, 6.2655000e-02,
+                     1.9545313e-03, 3.9045625e-03, 5.8845638e-03, 7.8089750e-03, -6.0151856e-02, 6.9784373e-03,
+                     -1.6634936e+03, -7.6505613e-04, 1.9545313e-03, 3.9045625e-03, 5.8845638e-03, 7.8089750e-03,
+                     1.5629950e-02, 1.5225650e-02, -3.1256500e-02, 9.3857500e-02, 7.9284608e-01, 2.8815269e-01,
+                     -1.1787039e-01, 6.1035156e-05, -1.1787039e-06, -1.0749481e-01, -1.3085605e+00, 6.5981364e-01,
+                     -7.0325255e-02, 2.7448297e-01, 5.5694544e-01, -2.3220782e-01, -5.9746221e-02, 15.23213444,
+                     -0.00004323, 1.9767435e-04, -1.2203161e+00, 2.9099861e-01, -7.9642259e-02, 1.3200364e+00,
+                     -1.5196867e+00, -1.2530587e+00, -2.0159689e-03, -1.9767643e+00, 6.0834163e-04, 7.8943473e-05,
+                     7.8247029e-04, -6.4658634e-05, -2.3020705e-06, -1.5630834e-05, -7.4762434e-07, 2.1336775e-06],
+                    dtype=np.float32)
+
+
+def write_fixture64(scalar, avx):
+    x = reference_fixture64()
+    assert x.size == 64
+    d = {"input": x.view(np.uint32)}
+    for mode in DET_MODES:
+        for s in (1.0, 3.7):
+            if mode.startswith("FLOAT16") and s != 1.0:
+                continue
+            d["%s@%g" % (mode, s)] = run(scalar, x, mode, s).view(np.uint32)
+    if avx is not None:
+        d["BFLOAT16_RNE@1"] = run(avx, x, "BFLOAT16_RNE").view(np.uint32)    # 64 = 4 AVX-512 vectors, no denormals
+    for mode in ("E5M2_RNE", "E4M3_RNE", "E3M4_RNE"):
+        d["%s@block16" % mode] = run(scalar, x, mode, 1.0, True, 16).view(np.uint32)
+    np.savez_compressed(os.path.join(OUT, "fixture64.npz"), **d)
+
+
 def run(ref, x, mode, scale=1.0, block_norm=False, block_size=1):
     t = torch.from_numpy(np.ascontiguousarray(x).copy())
     return ref.forward(t, mode, t.numel(), False, float(scale), block_norm, int(block_size))[0].numpy()
@@ -68,6 +103,9 @@ def main():
     scalar = ref_loader.load("fpemu_cpp_ref_scalar")
     avx = ref_loader.load("fpemu_cpp_ref_avx512")
     assert scalar is not None, "run oracle/build_ref.py cpu first"
+    write_fixture64(scalar, avx)
+    if sys.argv[1:] == ["fixture64"]:
+        return
 
     # 1. exhaustive fp16 patterns, scale 1: outputs are fp16-representable -> keep 16 bits
     pat = np.arange(65536, dtype=np.uint16).view(np.float16).astype(np.float32)

@@ -25,7 +25,7 @@ class OracleKernels(object):
         return out
 
     @staticmethod
-    def scale_from_amax(vec, flt_max):
+    def scale_from_amax(vec, flt_max, dtype=torch.float32):
         from oracle import fpemu_oracle as O
         return torch.tensor([O.scale_from_amax(float(a), flt_max) for a in vec], dtype=torch.float32)
 

@@ -145,3 +145,24 @@ def test_rand_bits_partition_independent():
     a = O.rand_bits(5, 0, 1000, O.FMT["BF16"])
     b = np.concatenate([O.rand_bits(5, 0, 501, O.FMT["BF16"]), O.rand_bits(5, 501, 499, O.FMT["BF16"])])
     assert np.array_equal(a, b)
+
+
+def test_reference_64_value_fixture(golden_dir):
+    """The input vector of the reference's own test script (mpemu/pytquant/test.py:120-135) through every
+    deterministic mode at scale 1 and 3.7, BFLOAT16 (AVX-512 build) and blocked mode with 16-element blocks."""
+    g = np.load(os.path.join(golden_dir, "fixture64.npz"))
+    x = g["input"].view(np.float32)
+    assert x.size == 64 and x[0] == 57344.0 and x[-1] == np.float32(2.1336775e-06)
+    seen = 0
+    for key in g.files:
+        if key == "input":
+            continue
+        mode, arg = key.split("@")
+        want = g[key].view(np.float32)
+        if arg.startswith("block"):
+            got = O.cast_blocked(x, mode, int(arg[5:]), unscale_fp32=True)
+        else:
+            got = O.cast(x, mode, scale=float(arg), unscale_fp32=True)
+        assert O.same_bits_or_both_nan(got, want).all(), key
+        seen += 1
+    assert seen >= 2 * 11 + 2 + 3

@@ -89,8 +89,59 @@ def test_rowwise_equals_per_row_amax_scaled_cast():
     x = (rng.standard_normal((16, 96)) * np.exp2(rng.integers(-4, 4, (16, 1)))).astype(np.float32)
     q, scales = O.cast_rowwise(x, "E4M3_RNE", 448.0)
     for r in range(16):
-        s = np.float32(448.0) / np.float32(np.abs(x[r]).max())
+        s = (np.float32(1.0) / np.float32(np.abs(x[r]).max())) * np.float32(448.0)   # torch: vmax.reciprocal() * flt_max
         assert scales[r] == s
         assert np.array_equal(q[r].view(np.uint32), O.cast(x[r], "E4M3_RNE", scale=float(s)).view(np.uint32))
     assert O.scale_from_amax(0.0, 448.0) == np.float32(6.55e4)             # amax 0 -> inf -> clamp, qutils.py:285
     assert O.scale_from_amax(1e-3, 448.0) == np.float32(6.55e4)            # 4.48e5 > 3.275e4 -> 6.55e4
+
+
+def test_scale_from_amax_is_what_torch_computes_for_flt_max_over_a_0dim_tensor():
+    """qutils.py:283-285 on the reference's own arithmetic: `flt_max / vmax` with vmax a 0-dim tensor (torch evaluates
+    Tensor.__rtruediv__ as reciprocal * flt_max in the tensor's dtype), then the clamp — float32 and float16, with a
+    dense sweep around the clamp threshold (the comparison runs in half for half tensors)."""
+    import torch
+    rng = np.random.default_rng(3)
+    for dtype, like in ((torch.float32, np.zeros(1, np.float32)), (torch.float16, np.zeros(1, np.float16))):
+        for flt_max in (448.0, 57344.0, 30.0):
+            edge = flt_max / 3.275e4
+            v = np.concatenate([rng.uniform(1e-3, 900.0, 1500), np.linspace(edge * 0.97, edge * 1.03, 800), [0.0]])
+            v = torch.from_numpy(v).to(dtype)
+            for t in v:
+                scale = flt_max / t
+                scale = 6.55e+04 if scale > 3.275e+04 else scale
+                got = O.scale_from_amax(float(t), flt_max, like=like)
+                assert got == float(scale), (dtype, flt_max, float(t), got, float(scale))
+                unclamped = O.scale_from_amax(float(t), flt_max, like=like, clamp=False)
+                assert unclamped == float(flt_max / t)                      # fine-grained branch, qutils.py:327-328
+
+
+def test_amax_propagates_nan_like_torch_max():
+    import torch
+    x = np.random.default_rng(1).standard_normal(1000).astype(np.float32)
+    assert O.amax(x) == torch.max(abs(torch.from_numpy(x))).item()
+    x[500] = np.nan
+    assert np.isnan(O.amax(x)) and np.isnan(torch.max(abs(torch.from_numpy(x))).item())
+    s = O.scale_from_amax(O.amax(x), 448.0)
+    assert np.isnan(s)                                                      # NaN > 3.275e4 is False: no clamp
+    assert np.isnan(O.cast(x, "E4M3_RNE", scale=s)).all() and np.isnan(O.cast(x, "E5M2_RNE", scale=s)).all()
+
+
+def test_scaled_branches_of_quantize_tensor_equal_the_reference_stack_golden(golden_dir):
+    """tests/golden/modules.npz holds outputs of the reference's own quantize_tensor (CPU op, fp32 un-scale); the
+    oracle's row loop must reproduce the per-tensor, per-channel and fine-grained branches bit for bit."""
+    import os
+    G = np.load(os.path.join(golden_dir, "modules.npz"))
+    O.set_nan_mode(True)
+    try:
+        w, a = G["qt_weight"], G["qt_act"]
+        for key, x, rows, fmax, clamp in (("qt|e4m3|rne|per-channel|1|qt_weight", w, 24, 448.0, True),
+                                          ("qt|e3m4|rne|per-channel|1|qt_weight", w, 24, 30.0, True),
+                                          ("qt|e4m3|rne|fine-grained|4|qt_weight", w, 24 * 4, 448.0, False),
+                                          ("qt|e4m3|rne|per-tensor|1|qt_act", a, 1, 448.0, True),
+                                          ("qt|e5m2|rne|per-tensor|1|qt_act", a, 1, 57344.0, True)):
+            mode = key.split("|")[1].upper() + "_RNE"
+            q, _ = O.cast_rowwise(x.reshape(rows, -1), mode, fmax, unscale_fp32=True, clamp=clamp)
+            assert np.array_equal(q.reshape(x.shape).view(np.uint32), G[key].view(np.uint32)), key
+    finally:
+        O.set_nan_mode(False)
