@@ -53,6 +53,17 @@ __device__ __forceinline__ int mt_find(const void* table, int count, uint32_t b)
   return s_idx;
 }
 
+// Scale of tensor t: the caller's d_scales[t], or — when the launch was given the vector of absolute maxima instead
+// (proto.d_amax) — derived here exactly as fpemu_scale_from_amax_dtype does, so that an amax-scaled sweep over a tensor
+// list needs no separate scale launch; the tensor's first CTA stores the scale it used into proto.d_scale_out[t].
+template <int DT>
+__device__ __forceinline__ float mt_scale(const CastArgs& proto, const float* d_scales, int t, bool first_cta) {
+  if (proto.d_amax == nullptr) return __ldg(d_scales + t);
+  const float s = scale_from_amax(__ldg(proto.d_amax + t), proto.flt_max, true, DT);
+  if (proto.d_scale_out != nullptr && first_cta && threadIdx.x == 0) proto.d_scale_out[t] = s;
+  return s;
+}
+
 template <int FMT, int RND, int DT, bool SCALED>
 __global__ void __launch_bounds__(kThreads) cast_multi_kernel(const void* table, const int count, const CastArgs proto,
                                                              const float* d_scales) {
@@ -68,15 +79,15 @@ __global__ void __launch_bounds__(kThreads) cast_multi_kernel(const void* table,
   ScaleCtx sc;
   sc.scale = 1.0f; sc.rscale = 1.0f;
   sc.unscale32 = (a.flags & FPEMU_FLAG_UNSCALE_FP32) != 0;
+  const int64_t local_cta = (int64_t)(blockIdx.x - e.cta_cast);
   if (SCALED) {
-    const float s = effective_scale(__ldg(d_scales + t), DT);
+    const float s = effective_scale(mt_scale<DT>(proto, d_scales, t, local_cta == 0), DT);
     sc.scale = s;
     sc.rscale = __frcp_rn(s);
   }
   const int64_t nvec = a.n / VE;
   const char* in = static_cast<const char*>(a.in);
   char* out = static_cast<char*>(a.out);
-  const int64_t local_cta = (int64_t)(blockIdx.x - e.cta_cast);
   const int64_t base = local_cta * (kThreads * U) + threadIdx.x;
   Vec32 v[U];
 #pragma unroll
@@ -134,12 +145,12 @@ __global__ void __launch_bounds__(kThreads) encode_multi_kernel(const void* tabl
   a = with_device_seed(a);
   ScaleCtx sc;
   sc.scale = 1.0f; sc.rscale = 1.0f; sc.unscale32 = false;
+  const int64_t local_cta = (int64_t)(blockIdx.x - e.cta_cast);
   if (SCALED) {
-    const float s = effective_scale(__ldg(d_scales + t), DT);
+    const float s = effective_scale(mt_scale<DT>(proto, d_scales, t, local_cta == 0), DT);
     sc.scale = s;
     sc.rscale = __frcp_rn(s);
   }
-  const int64_t local_cta = (int64_t)(blockIdx.x - e.cta_cast);
   const int64_t ctas_of_t = (a.n / VE + kThreads * U - 1) / (kThreads * U);
   encode_cta<FMT, RND, false, DT, SCALED, U>(a, sc, local_cta, local_cta == (ctas_of_t > 0 ? ctas_of_t - 1 : 0));
 }
@@ -275,22 +286,37 @@ extern "C" int fpemu_amax_multi(const void* d_table, const void* h_table, int co
   return (int)cudaGetLastError();
 }
 
-extern "C" int fpemu_cast_multi(const void* d_table, const void* h_table, int count, int format, int rounding, int flags,
-                                const float* d_scales, uint64_t seed, void* stream_) {
+namespace {
+
+// Shared body of the four list launches: values or codes, scales given or derived from a vector of maxima.
+int launch_multi(bool codes, const void* d_table, const void* h_table, int count, int format, int rounding, int flags,
+                 const float* d_scales, const float* d_amax, float flt_max, float* d_scales_out, uint64_t seed,
+                 void* stream_) {
   if (d_table == nullptr || h_table == nullptr || count <= 0) return FPEMU_ERR_ARG;
   const MtHeader* h = static_cast<const MtHeader*>(h_table);
   if (h->count != count) return FPEMU_ERR_ARG;
   if (format < 0 || format >= FPEMU_FMT_COUNT || rounding < 0 || rounding >= FPEMU_RND_COUNT) return FPEMU_ERR_MODE;
   if (flags & FPEMU_FLAG_DAZ) return FPEMU_ERR_MODE;             // DAZ variants: use the per-tensor entry point
-  const bool scaled = d_scales != nullptr && format != FPEMU_FMT_BF16 && format != FPEMU_FMT_FP16;
+  const bool takes_scale = format != FPEMU_FMT_BF16 && format != FPEMU_FMT_FP16;
+  if (d_amax != nullptr && !takes_scale) return FPEMU_ERR_MODE;
+  const bool scaled = (d_scales != nullptr || d_amax != nullptr) && takes_scale;
   MultiCastKernel k = nullptr;
-  switch (format) {
-    case FPEMU_FMT_E5M2: k = mpick_rnd<FPEMU_FMT_E5M2>(rounding, h->dtype, scaled); break;
-    case FPEMU_FMT_E4M3: k = mpick_rnd<FPEMU_FMT_E4M3>(rounding, h->dtype, scaled); break;
-    case FPEMU_FMT_E3M4: k = mpick_rnd<FPEMU_FMT_E3M4>(rounding, h->dtype, scaled); break;
-    case FPEMU_FMT_BF16: k = mpick_rnd<FPEMU_FMT_BF16>(rounding, h->dtype, false); break;
-    case FPEMU_FMT_FP16: k = mpick_rnd<FPEMU_FMT_FP16>(rounding, h->dtype, false); break;
-    default: break;
+  if (codes) {
+    switch (format) {
+      case FPEMU_FMT_E5M2: k = epick_rnd<FPEMU_FMT_E5M2>(rounding, h->dtype, scaled); break;
+      case FPEMU_FMT_E4M3: k = epick_rnd<FPEMU_FMT_E4M3>(rounding, h->dtype, scaled); break;
+      case FPEMU_FMT_E3M4: k = epick_rnd<FPEMU_FMT_E3M4>(rounding, h->dtype, scaled); break;
+      default: break;                                            // only the three 8-bit formats have codes
+    }
+  } else {
+    switch (format) {
+      case FPEMU_FMT_E5M2: k = mpick_rnd<FPEMU_FMT_E5M2>(rounding, h->dtype, scaled); break;
+      case FPEMU_FMT_E4M3: k = mpick_rnd<FPEMU_FMT_E4M3>(rounding, h->dtype, scaled); break;
+      case FPEMU_FMT_E3M4: k = mpick_rnd<FPEMU_FMT_E3M4>(rounding, h->dtype, scaled); break;
+      case FPEMU_FMT_BF16: k = mpick_rnd<FPEMU_FMT_BF16>(rounding, h->dtype, false); break;
+      case FPEMU_FMT_FP16: k = mpick_rnd<FPEMU_FMT_FP16>(rounding, h->dtype, false); break;
+      default: break;
+    }
   }
   if (k == nullptr) return FPEMU_ERR_MODE;                       // rare modes: use the per-tensor entry point
   if (h->total_cast == 0) return FPEMU_OK;
@@ -300,35 +326,35 @@ extern "C" int fpemu_cast_multi(const void* d_table, const void* h_table, int co
   proto.seed_lo = (uint32_t)seed; proto.seed_hi = (uint32_t)(seed >> 32);
   proto.elem_offset = 0;
   proto.fmt = format; proto.rnd = rounding; proto.flags = flags;
-  proto.d_amax = nullptr; proto.flt_max = 0.0f; proto.d_scale_out = nullptr; proto.d_seed = seed_source();
+  proto.d_amax = d_amax; proto.flt_max = flt_max; proto.d_scale_out = d_scales_out; proto.d_seed = seed_source();
   k<<<h->total_cast, kThreads, 0, static_cast<cudaStream_t>(stream_)>>>(d_table, count, proto, d_scales);
   return (int)cudaGetLastError();
 }
 
+}  // namespace
+
+extern "C" int fpemu_cast_multi(const void* d_table, const void* h_table, int count, int format, int rounding, int flags,
+                                const float* d_scales, uint64_t seed, void* stream_) {
+  return launch_multi(false, d_table, h_table, count, format, rounding, flags, d_scales, nullptr, 0.0f, nullptr, seed, stream_);
+}
+
 extern "C" int fpemu_encode_multi(const void* d_table, const void* h_table, int count, int format, int rounding, int flags,
                                   const float* d_scales, uint64_t seed, void* stream_) {
-  if (d_table == nullptr || h_table == nullptr || count <= 0) return FPEMU_ERR_ARG;
-  const MtHeader* h = static_cast<const MtHeader*>(h_table);
-  if (h->count != count) return FPEMU_ERR_ARG;
-  if (rounding < 0 || rounding >= FPEMU_RND_COUNT) return FPEMU_ERR_MODE;
-  if (flags & FPEMU_FLAG_DAZ) return FPEMU_ERR_MODE;             // DAZ variants: use the per-tensor entry point
-  const bool scaled = d_scales != nullptr;
-  MultiCastKernel k = nullptr;
-  switch (format) {
-    case FPEMU_FMT_E5M2: k = epick_rnd<FPEMU_FMT_E5M2>(rounding, h->dtype, scaled); break;
-    case FPEMU_FMT_E4M3: k = epick_rnd<FPEMU_FMT_E4M3>(rounding, h->dtype, scaled); break;
-    case FPEMU_FMT_E3M4: k = epick_rnd<FPEMU_FMT_E3M4>(rounding, h->dtype, scaled); break;
-    default: break;                                              // only the three 8-bit formats have codes
-  }
-  if (k == nullptr) return FPEMU_ERR_MODE;
-  if (h->total_cast == 0) return FPEMU_OK;
-  CastArgs proto;
-  proto.in = nullptr; proto.out = nullptr; proto.n = 0;
-  proto.scale = 1.0f; proto.d_scale = nullptr;
-  proto.seed_lo = (uint32_t)seed; proto.seed_hi = (uint32_t)(seed >> 32);
-  proto.elem_offset = 0;
-  proto.fmt = format; proto.rnd = rounding; proto.flags = flags;
-  proto.d_amax = nullptr; proto.flt_max = 0.0f; proto.d_scale_out = nullptr; proto.d_seed = seed_source();
-  k<<<h->total_cast, kThreads, 0, static_cast<cudaStream_t>(stream_)>>>(d_table, count, proto, d_scales);
-  return (int)cudaGetLastError();
+  return launch_multi(true, d_table, h_table, count, format, rounding, flags, d_scales, nullptr, 0.0f, nullptr, seed, stream_);
+}
+
+extern "C" int fpemu_cast_multi_amax(const void* d_table, const void* h_table, int count, int format, int rounding,
+                                     int flags, const float* d_amax, float flt_max, float* d_scales_out, uint64_t seed,
+                                     void* stream_) {
+  if (d_amax == nullptr) return FPEMU_ERR_ARG;
+  return launch_multi(false, d_table, h_table, count, format, rounding, flags, nullptr, d_amax, flt_max, d_scales_out, seed,
+                      stream_);
+}
+
+extern "C" int fpemu_encode_multi_amax(const void* d_table, const void* h_table, int count, int format, int rounding,
+                                       int flags, const float* d_amax, float flt_max, float* d_scales_out, uint64_t seed,
+                                       void* stream_) {
+  if (d_amax == nullptr) return FPEMU_ERR_ARG;
+  return launch_multi(true, d_table, h_table, count, format, rounding, flags, nullptr, d_amax, flt_max, d_scales_out, seed,
+                      stream_);
 }

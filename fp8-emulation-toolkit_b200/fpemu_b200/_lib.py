@@ -35,6 +35,7 @@ SIGNATURES = {
     "fpemu_cast_multi": (_i32, [_vp, _vp, _i32, _i32, _i32, _i32, _vp, _u64, _vp]),
     "fpemu_cast_amax_scaled_noalloc": (_i32, [_vp, _vp, _i64, _i32, _i32, _i32, _i32, _f32, _u64, _u64, _vp]),
     "fpemu_cast_host": (_i32, [_vp, _vp, _i64, _i32, _i32, _i32, _i32, _f32, _u64, _vp, _vp, _i64, _vp, _vp, _vp]),
+    "fpemu_cast_host_multi": (_i32, [_vp, _i64, _i32, _vp, _i32, _vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp]),
     "fpemu_fused_work_floats": (_i32, []),
     "fpemu_cast_amax_scaled_fused": (_i32, [_vp, _vp, _i64, _i32, _i32, _i32, _i32, _f32, _vp, _i32, _u64, _u64, _vp]),
     "fpemu_cast_rows_scaled": (_i32, [_vp, _vp, _i64, _i64, _i32, _i32, _i32, _i32, _vp, _u64, _u64, _vp]),
@@ -43,6 +44,8 @@ SIGNATURES = {
     "fpemu_set_seed_source": (_i32, [_vp]),
     "fpemu_advance_seed_source": (_i32, [_vp]),
     "fpemu_encode_multi": (_i32, [_vp, _vp, _i32, _i32, _i32, _i32, _vp, _u64, _vp]),
+    "fpemu_cast_multi_amax": (_i32, [_vp, _vp, _i32, _i32, _i32, _i32, _vp, _f32, _vp, _u64, _vp]),
+    "fpemu_encode_multi_amax": (_i32, [_vp, _vp, _i32, _i32, _i32, _i32, _vp, _f32, _vp, _u64, _vp]),
     "fpemu_encode": (_i32, [_vp, _vp, _i64, _i32, _i32, _i32, _i32, _f32, _vp, _u64, _u64, _vp]),
     "fpemu_decode": (_i32, [_vp, _vp, _i64, _i32, _i32, _i32, _f32, _vp, _vp]),
 }

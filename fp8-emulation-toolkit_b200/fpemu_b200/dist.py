@@ -49,67 +49,94 @@ def global_amax(slabs, group=None, kernels=CudaKernels, out=None):
     return vec
 
 
+def _sharded_amax_scaled(slabs, mode, row_offsets, cols, outs, group, seed, flt_max, kernels, pipeline, apply_one):
+    fmt, _, _ = L.parse_mode(mode)
+    if flt_max is None:
+        flt_max = _ops.FLT_MAX[fmt]
+    n = len(slabs)
+    row_offsets = row_offsets or [0] * n
+    cols = cols or [(x.shape[-1] if x.dim() > 1 else 1) for x in slabs]
+    world, _ = _world(group)
+    vec = torch.zeros(n, dtype=torch.float32, device=slabs[0].device)
+    scales = torch.empty(n, dtype=torch.float32, device=slabs[0].device)
+    results = [None] * n
+
+    def amax_run(t0, t1):
+        for t in range(t0, t1):
+            if slabs[t].numel():
+                kernels.amax(slabs[t], out=vec[t:t + 1])
+
+    def reduce_run(t0, t1):
+        if world > 1:
+            return dist.all_reduce(vec[t0:t1], op=dist.ReduceOp.MAX, group=group, async_op=True)
+        return None
+
+    def apply_run(t0, t1):
+        scales[t0:t1] = kernels.scale_from_amax(vec[t0:t1], flt_max, dtype=slabs[0].dtype)
+        for t in range(t0, t1):
+            results[t] = apply_one(t, slabs[t], None if outs is None else outs[t], scales[t:t + 1], seed + t,
+                                   row_offsets[t] * cols[t])
+
+    _ops.pipelined_sweep(_ops.split_runs([x.numel() for x in slabs], pipeline if world > 1 else 1),
+                         amax_run, reduce_run, apply_run)
+    return results, scales
+
+
 def sharded_amax_scaled_cast(slabs, mode, row_offsets=None, cols=None, outs=None, group=None, seed=0,
-                             flt_max=None, kernels=CudaKernels, unscale_fp32=False):
+                             flt_max=None, kernels=CudaKernels, unscale_fp32=False, pipeline=1):
     """Per-tensor amax-scaled cast of row-sharded tensors.
 
     slabs        list of this rank's slabs (contiguous; slab t holds rows [row_offsets[t], ...) of tensor t)
     row_offsets  first global row of each slab (default 0: unsharded); cols: row length of each tensor
     outs         optional preallocated outputs (pass the slabs themselves for in-place)
+    pipeline     k > 1: the list is cut into k runs whose all-reduces overlap the neighbouring runs' kernels
+                 (fpemu_b200.ops.pipelined_sweep); results do not depend on k
     Returns (outs, scales) where scales is the float32 device vector of per-tensor scales."""
-    fmt, _, _ = L.parse_mode(mode)
-    if flt_max is None:
-        flt_max = _ops.FLT_MAX[fmt]
-    n = len(slabs)
-    row_offsets = row_offsets or [0] * n
-    cols = cols or [(x.shape[-1] if x.dim() > 1 else 1) for x in slabs]
-    amax_vec = global_amax(slabs, group=group, kernels=kernels)
-    scales = kernels.scale_from_amax(amax_vec, flt_max, dtype=slabs[0].dtype)
-    results = []
-    for t, x in enumerate(slabs):
-        out = None if outs is None else outs[t]
-        results.append(kernels.cast(x, mode, out=out, d_scale=scales[t:t + 1], seed=seed + t,
-                                    elem_offset=row_offsets[t] * cols[t], unscale_fp32=unscale_fp32))
-    return results, scales
+    return _sharded_amax_scaled(
+        slabs, mode, row_offsets, cols, outs, group, seed, flt_max, kernels, pipeline,
+        lambda t, x, out, d_scale, sd, off: kernels.cast(x, mode, out=out, d_scale=d_scale, seed=sd, elem_offset=off,
+                                                         unscale_fp32=unscale_fp32))
 
 
 def sharded_amax_scaled_encode(slabs, mode, row_offsets=None, cols=None, outs=None, group=None, seed=0,
-                               flt_max=None, kernels=CudaKernels):
+                               flt_max=None, kernels=CudaKernels, pipeline=1):
     """As sharded_amax_scaled_cast, but every rank ends up with the 8-bit codes of its slabs (uint8) plus the common
-    float32[T] scale vector — the wire form of a row-sharded weight set.  Same single all-reduce(MAX)."""
-    fmt, _, _ = L.parse_mode(mode)
-    if flt_max is None:
-        flt_max = _ops.FLT_MAX[fmt]
-    n = len(slabs)
-    row_offsets = row_offsets or [0] * n
-    cols = cols or [(x.shape[-1] if x.dim() > 1 else 1) for x in slabs]
-    scales = kernels.scale_from_amax(global_amax(slabs, group=group, kernels=kernels), flt_max, dtype=slabs[0].dtype)
-    codes = [kernels.encode(x, mode, out=None if outs is None else outs[t], d_scale=scales[t:t + 1], seed=seed + t,
-                            elem_offset=row_offsets[t] * cols[t], expect_normals=True) for t, x in enumerate(slabs)]
-    return codes, scales
+    float32[T] scale vector — the wire form of a row-sharded weight set.  Same all-reduce(MAX)."""
+    return _sharded_amax_scaled(
+        slabs, mode, row_offsets, cols, outs, group, seed, flt_max, kernels, pipeline,
+        lambda t, x, out, d_scale, sd, off: kernels.encode(x, mode, out=out, d_scale=d_scale, seed=sd, elem_offset=off,
+                                                           expect_normals=True))
 
 
 class ShardedPlan(object):
     """The multi-tensor version of sharded_amax_scaled_cast: the slab list is described to the library once and
-    every sweep is then three launches (amax, scale, cast) plus ONE all-reduce(MAX) over the float32[T] vector,
-    instead of 2T + 1 launches.  This is what makes the whole-model sweep scale past a few GPUs, where the
-    per-tensor version becomes launch-bound (tools/llama7b_sweep.py)."""
+    every sweep is then two launches per run of tensors (amax, cast — the cast kernel derives the scales) plus ONE
+    all-reduce(MAX) per run over its slice of the float32[T] vector, instead of 2T + 1 launches.  With `pipeline` = k
+    the list is cut into k consecutive runs and each run's all-reduce is issued asynchronously right after its amax
+    launch, so it executes behind the next run's amax / the previous run's cast instead of idling the GPU between
+    two kernels (tools/llama7b_sweep.py measures k = 1, 2, 4)."""
 
-    def __init__(self, slabs, row_offsets=None, cols=None, outs=None, group=None):
+    def __init__(self, slabs, row_offsets=None, cols=None, outs=None, group=None, pipeline=2):
         n = len(slabs)
         row_offsets = row_offsets or [0] * n
         cols = cols or [(x.shape[-1] if x.dim() > 1 else 1) for x in slabs]
         self.group = group
+        self.pipeline = pipeline
         self.plan = _ops.MultiTensorPlan(slabs, outs, [r * c for r, c in zip(row_offsets, cols)])
 
     def _allreduce(self, vec):
         world, _ = _world(self.group)
         if world > 1:
-            dist.all_reduce(vec, op=dist.ReduceOp.MAX, group=self.group)
+            return dist.all_reduce(vec, op=dist.ReduceOp.MAX, group=self.group, async_op=True)
+        return None
+
+    def _depth(self):
+        world, _ = _world(self.group)
+        return self.pipeline if world > 1 else 1
 
     def amax_scaled_cast(self, mode, seed=0, flt_max=None, unscale_fp32=False):
         return self.plan.amax_scaled_cast(mode, flt_max=flt_max, seed=seed, reduce_fn=self._allreduce,
-                                          unscale_fp32=unscale_fp32)
+                                          unscale_fp32=unscale_fp32, pipeline=self._depth())
 
     def cast(self, mode, seed=0):
         return self.plan.cast(mode, seed=seed)
@@ -117,7 +144,8 @@ class ShardedPlan(object):
     def amax_scaled_encode(self, mode, seed=0, flt_max=None):
         """As amax_scaled_cast, for a plan whose outputs are uint8 code buffers: every rank ends up with the 8-bit
         codes of its slabs and the same float32[T] scale vector."""
-        return self.plan.amax_scaled_encode(mode, flt_max=flt_max, seed=seed, reduce_fn=self._allreduce)
+        return self.plan.amax_scaled_encode(mode, flt_max=flt_max, seed=seed, reduce_fn=self._allreduce,
+                                            pipeline=self._depth())
 
 
 def sharded_cast(slabs, mode, row_offsets=None, cols=None, outs=None, scale=1.0, seed=0, kernels=CudaKernels):

@@ -474,6 +474,36 @@ def decode_rowwise(codes, scales, mode, dtype=torch.float32, out=None, unscale_f
     return out
 
 
+def split_runs(sizes, depth):
+    """Cut a list of tensor sizes into `depth` consecutive runs [(first, one past last)] of about equal total size
+    (every run gets at least one tensor)."""
+    count, total = len(sizes), sum(sizes)
+    depth = max(1, min(int(depth), count))
+    runs, t0, acc, k = [], 0, 0, 1
+    for t, n in enumerate(sizes):
+        acc += n
+        left = count - (t + 1)
+        if t == count - 1 or (k < depth and ((acc * depth >= total * k and left >= depth - k) or left == depth - k)):
+            runs.append((t0, t + 1))
+            t0, k = t + 1, k + 1
+    return runs
+
+
+def pipelined_sweep(runs, amax_fn, reduce_fn, apply_fn):
+    """The schedule of an amax-scaled sweep whose maxima need an exchange step: for every run, reduce locally
+    (amax_fn) and start its exchange (reduce_fn may return an object with .wait(), i.e. an asynchronous collective);
+    then, run by run, wait for the exchange and apply (apply_fn).  Run i's exchange therefore executes while run
+    i+1 is being reduced and run i-1 is being cast."""
+    pending = []
+    for t0, t1 in runs:
+        amax_fn(t0, t1)
+        pending.append(reduce_fn(t0, t1) if reduce_fn is not None else None)
+    for (t0, t1), work in zip(runs, pending):
+        if work is not None:
+            work.wait()                  # stream-ordered for NCCL work objects: the host does not block
+        apply_fn(t0, t1)
+
+
 class MultiTensorPlan(object):
     """A fixed list of CUDA tensors (same dtype, same device) that is reduced / cast with ONE launch each.
 
@@ -500,6 +530,7 @@ class MultiTensorPlan(object):
         if not self.packed and any(y.dtype != dt for y in outs):
             raise ValueError("fpemu: outputs must be all of the input dtype (cast) or all uint8 (encode)")
         self.ins, self.outs, self.count, self.device, self.dtype = ins, outs, len(ins), dev, dt
+        self.offsets = offs
 
         class Desc(ctypes.Structure):
             _fields_ = [("inp", ctypes.c_void_p), ("out", ctypes.c_void_p), ("n", ctypes.c_int64),
@@ -513,6 +544,8 @@ class MultiTensorPlan(object):
         L.check(st, "fpemu_multi_table_build")
         self.d_table = self.h_table.to(dev)
         self.elements = sum(x.numel() for x in ins)
+        self._amax_vec = None          # float32[count] reused by the amax-scaled sweeps
+        self._parts = {}               # pipeline depth -> {(first tensor, one past the last): sub-plan}
 
     def amax(self, out=None):
         """float32[count] vector of max|tensor t| (max-accumulated into `out` when given), one launch."""
@@ -546,16 +579,6 @@ class MultiTensorPlan(object):
         L.check(st, "fpemu_encode_multi(%s)" % mode)
         return self.outs
 
-    def amax_scaled_encode(self, mode, flt_max=None, seed=None, reduce_fn=None):
-        """Per-tensor amax-scaled 8-bit codes for the whole list: amax launch -> [reduce_fn] -> scale launch ->
-        encode launch.  Returns (codes, scales); `decode(codes[t], fmt, scale=scales[t])` gives the cast's values."""
-        fmt, _, _ = L.parse_mode(mode)
-        vec = self.amax()
-        if reduce_fn is not None:
-            reduce_fn(vec)
-        scales = scale_from_amax(vec, FLT_MAX[fmt] if flt_max is None else flt_max, dtype=self.dtype)
-        return self.encode(mode, d_scales=scales, seed=seed, expect_normals=True), scales   # scaled to the maximum
-
     def cast(self, mode, d_scales=None, seed=None, unscale_fp32=False):
         """Cast every tensor in one launch; tensor t uses d_scales[t] (None: scale 1) and seed + t."""
         if self.packed:
@@ -565,33 +588,80 @@ class MultiTensorPlan(object):
             flags |= L.FLAG_UNSCALE_FP32
         if rnd == L.RND_STOCHASTIC and seed is None:
             seed = next_seed()
-        sp = None
-        if d_scales is not None:
-            if not (d_scales.is_cuda and d_scales.dtype == torch.float32 and d_scales.numel() >= self.count):
-                raise ValueError("fpemu: d_scales must be a float32 CUDA vector with one entry per tensor")
-            sp = d_scales.data_ptr()
         with _on_device(self.d_table):
             st = L.lib().fpemu_cast_multi(self.d_table.data_ptr(), self.h_table.data_ptr(), self.count, fmt, rnd, flags,
-                                          sp, int(seed or 0), _stream(self.d_table))
+                                          self._scales_ptr(d_scales), int(seed or 0), _stream(self.d_table))
         L.check(st, "fpemu_cast_multi(%s)" % mode)
         return self.outs
 
-    def amax_scaled_cast(self, mode, flt_max=None, seed=None, reduce_fn=None, unscale_fp32=False):
-        """Per-tensor amax-scaled cast of the whole list: amax launch -> [reduce_fn(amax_vec), e.g. an all-reduce]
-        -> scale launch -> cast launch.  Returns (outs, scales)."""
-        fmt, _, _ = L.parse_mode(mode)
+    def _from_amax(self, mode, d_amax, flt_max, d_scales_out, seed, flags_extra=0):
+        """The second launch of an amax-scaled sweep: cast (or encode) every tensor with the scale the kernel derives
+        from d_amax[t] (no separate scale launch); the scales used land in d_scales_out."""
+        fmt, rnd, flags = L.parse_mode(mode)
+        fn = L.lib().fpemu_encode_multi_amax if self.packed else L.lib().fpemu_cast_multi_amax
+        with _on_device(self.d_table):
+            st = fn(self.d_table.data_ptr(), self.h_table.data_ptr(), self.count, fmt, rnd, flags | flags_extra,
+                    d_amax.data_ptr(), float(flt_max), d_scales_out.data_ptr(), int(seed) & 0xFFFFFFFFFFFFFFFF,
+                    _stream(self.d_table))
+        L.check(st, "fpemu_%s_multi_amax(%s)" % ("encode" if self.packed else "cast", mode))
+
+    def _pipeline_parts(self, depth):
+        """The tensor list cut into `depth` consecutive runs of about equal size, each with its own table, so that the
+        exchange step of one run (an all-reduce of its maxima) overlaps the reduction / cast of its neighbours."""
+        depth = max(1, min(int(depth), self.count))
+        parts = self._parts.get(depth)
+        if parts is None:
+            if depth == 1:
+                parts = {(0, self.count): self}
+            else:
+                parts = {(t0, t1): MultiTensorPlan(self.ins[t0:t1], self.outs[t0:t1], self.offsets[t0:t1])
+                         for t0, t1 in split_runs([x.numel() for x in self.ins], depth)}
+            self._parts[depth] = parts
+        return parts
+
+    def _amax_scaled(self, mode, flt_max, seed, reduce_fn, pipeline, flags_extra):
+        fmt, rnd, _ = L.parse_mode(mode)
         if flt_max is None:
             flt_max = FLT_MAX[fmt]
-        vec = self.amax()
-        if reduce_fn is not None:
-            reduce_fn(vec)
-        scales = scale_from_amax(vec, flt_max, dtype=self.dtype)
-        return self.cast(mode, d_scales=scales, seed=seed, unscale_fp32=unscale_fp32), scales
+        if rnd == L.RND_STOCHASTIC and seed is None:
+            seed = next_seed()
+        seed = int(seed or 0)
+        if self._amax_vec is None:
+            self._amax_vec = torch.empty(self.count, dtype=torch.float32, device=self.device)
+        vec = self._amax_vec
+        scales = torch.empty(self.count, dtype=torch.float32, device=self.device)
+        vec.zero_()
+        parts = self._pipeline_parts(pipeline if reduce_fn is not None else 1)
+        pipelined_sweep(sorted(parts),
+                        lambda t0, t1: parts[(t0, t1)].amax(out=vec[t0:t1]),
+                        None if reduce_fn is None else (lambda t0, t1: reduce_fn(vec[t0:t1])),
+                        lambda t0, t1: parts[(t0, t1)]._from_amax(mode, vec[t0:t1], flt_max, scales[t0:t1], seed + t0,
+                                                                  flags_extra))
+        return self.outs, scales
+
+    def amax_scaled_encode(self, mode, flt_max=None, seed=None, reduce_fn=None, pipeline=1):
+        """Per-tensor amax-scaled 8-bit codes for the whole list: amax launch -> [reduce_fn] -> encode launch (which
+        derives the scales itself).  Returns (codes, scales); `decode(codes[t], fmt, scale=scales[t])` gives the
+        cast's values.  `reduce_fn` / `pipeline`: see amax_scaled_cast."""
+        if not self.packed:
+            raise ValueError("fpemu: this plan's outputs are not uint8 code buffers")
+        return self._amax_scaled(mode, flt_max, seed, reduce_fn, pipeline, L.FLAG_EXPECT_NORMALS)   # scaled to the maximum
+
+    def amax_scaled_cast(self, mode, flt_max=None, seed=None, reduce_fn=None, unscale_fp32=False, pipeline=1):
+        """Per-tensor amax-scaled cast of the whole list in TWO launches: amax -> [reduce_fn(amax_vec)] -> cast (the
+        cast kernel derives every tensor's scale from its maximum).  Returns (outs, scales).
+        `reduce_fn(vec)` reduces the float32 vector of maxima in place across ranks (an all-reduce MAX); it may return
+        an object with `.wait()` (an asynchronous collective).  `pipeline` = k > 1 cuts the list into k consecutive
+        runs and issues run i's all-reduce before run i+1's amax launch, so the collective runs behind the
+        reductions / casts of the neighbouring runs instead of between two kernels; results are identical."""
+        if self.packed:
+            raise ValueError("fpemu: this plan's outputs are uint8 code buffers: use amax_scaled_encode()")
+        return self._amax_scaled(mode, flt_max, seed, reduce_fn, pipeline, L.FLAG_UNSCALE_FP32 if unscale_fp32 else 0)
 
 
 class HostCaster(object):
-    """Host-buffer cast (pinned in, pinned out) pipelined through two device staging buffers.
-    Owns the staging buffers and three streams; `run` is what the end-to-end benchmark times."""
+    """Host-buffer casts (pinned in, pinned out) pipelined through device staging buffers.
+    Owns the staging buffers and three streams; `run` / `run_multi` are what the end-to-end benchmark times."""
 
     def __init__(self, dtype=torch.float32, chunk_elems=1 << 24, device=None):
         self.device = torch.device("cuda", torch.cuda.current_device() if device is None else device)
@@ -599,6 +669,8 @@ class HostCaster(object):
         self.chunk = int(chunk_elems) // 16 * 16
         self.stage = [torch.empty(self.chunk, dtype=dtype, device=self.device) for _ in range(2)]
         self.streams = [torch.cuda.Stream(self.device) for _ in range(3)]
+        self.resident = None               # device copy of the input for run_multi, grown on demand
+        self.work = torch.zeros(2, dtype=torch.float32, device=self.device)
 
     def run(self, h_in, h_out, mode, scale=1.0, seed=0):
         if h_in.is_cuda or h_out.is_cuda:
@@ -611,3 +683,38 @@ class HostCaster(object):
                                          self.streams[1].cuda_stream, self.streams[2].cuda_stream)
         L.check(st, "fpemu_cast_host(%s)" % mode)
         return h_out
+
+    def run_multi(self, h_in, jobs):
+        """Several casts of one host tensor with ONE upload: `jobs` is a list of (h_out, mode, scale, seed) where
+        `scale` is a float or the string "amax" (per-tensor amax-scaled, mpemu/qutils.py:274-287).  Returns the list
+        of output tensors.  Synchronises its three streams before returning."""
+        import ctypes
+
+        class Job(ctypes.Structure):
+            _fields_ = [("h_out", ctypes.c_void_p), ("format", ctypes.c_int), ("rounding", ctypes.c_int),
+                        ("flags", ctypes.c_int), ("scale", ctypes.c_float), ("amax_scaled", ctypes.c_int),
+                        ("flt_max", ctypes.c_float), ("seed", ctypes.c_uint64)]
+        if h_in.is_cuda or not h_in.is_contiguous() or h_in.dtype != self.dtype:
+            raise ValueError("HostCaster.run_multi takes a contiguous host tensor of the caster's dtype")
+        n = h_in.numel()
+        arr = (Job * len(jobs))()
+        for i, (h_out, mode, scale, seed) in enumerate(jobs):
+            if h_out.is_cuda or not h_out.is_contiguous() or h_out.dtype != self.dtype or h_out.numel() < n:
+                raise ValueError("HostCaster.run_multi: outputs must be contiguous host tensors of the input's dtype and size")
+            fmt, rnd, flags = L.parse_mode(mode)
+            amax = isinstance(scale, str)
+            if amax and scale != "amax":
+                raise ValueError("scale must be a number or 'amax'")
+            arr[i].h_out, arr[i].format, arr[i].rounding, arr[i].flags = h_out.data_ptr(), fmt, rnd, flags
+            arr[i].scale, arr[i].amax_scaled = (1.0 if amax else float(scale)), int(amax)
+            arr[i].flt_max, arr[i].seed = FLT_MAX.get(fmt, 0.0), int(seed)
+        if self.resident is None or self.resident.numel() < n:
+            self.resident = torch.empty(n, dtype=self.dtype, device=self.device)
+        with _on_device(self.stage[0]):
+            st = L.lib().fpemu_cast_host_multi(h_in.data_ptr(), n, _DT[self.dtype], ctypes.addressof(arr), len(jobs),
+                                               self.resident.data_ptr(), self.stage[0].data_ptr(),
+                                               self.stage[1].data_ptr(), self.work.data_ptr(), self.chunk,
+                                               self.streams[0].cuda_stream, self.streams[1].cuda_stream,
+                                               self.streams[2].cuda_stream)
+        L.check(st, "fpemu_cast_host_multi")
+        return [j[0] for j in jobs]

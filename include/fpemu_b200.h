@@ -233,6 +233,27 @@ FPEMU_API int fpemu_cast_host(const void* h_in, void* h_out, int64_t n, int dtyp
                     int flags, float scale, uint64_t seed, void* d_stage0, void* d_stage1,
                     int64_t chunk_elems, void* stream_h2d, void* stream_compute, void* stream_d2h);
 
+/* Several casts of ONE host tensor (a format x rounding sweep over the same input, with or without per-tensor
+ * amax-scaled members): the input crosses the bus once.  Chunks of chunk_elems elements are uploaded into d_in (a device
+ * buffer of n elements that keeps the whole input resident), every chunk is cast once per job into the two-slot
+ * staging ring d_stage0 / d_stage1 (chunk_elems elements each) and copied to that job's h_out; jobs with
+ * amax_scaled != 0 use scale = the scale of fpemu_scale_from_amax_dtype for max|input| (reduced chunk by chunk while the
+ * other jobs run, then cast in a second pass over d_in; d_work: one device float, required when such a job exists).
+ * Same streams, overlap and final synchronisation as fpemu_cast_host.  Bus traffic 1 x H2D + njobs x D2H.
+ * Replaces M round trips `x.cuda(); forward(mode_i); .cpu()` (and, for amax-scaled jobs, the per-tensor branch of
+ * quantize_tensor, mpemu/qutils.py:274-287) of a CPU-resident caller. */
+typedef struct fpemu_host_job {
+  void* h_out;       /* host output, n elements                                              */
+  int format, rounding, flags;
+  float scale;       /* host scale (ignored when amax_scaled)                                */
+  int amax_scaled;   /* != 0: scale derived from max|input| with flt_max                     */
+  float flt_max;
+  uint64_t seed;     /* stochastic rounding: Philox key; element i of the tensor uses index i */
+} fpemu_host_job;
+FPEMU_API int fpemu_cast_host_multi(const void* h_in, int64_t n, int dtype, const fpemu_host_job* jobs, int njobs,
+                                    void* d_in, void* d_stage0, void* d_stage1, float* d_work, int64_t chunk_elems,
+                                    void* stream_h2d, void* stream_compute, void* stream_d2h);
+
 /* ---- multi-tensor launches: one amax launch and one cast launch for a whole list of tensors -----------------
  * Replaces the reference's tensor-by-tensor Python loops (mpemu/qutils.py:470-475 quantize_model_weights,
  * mpemu/hybrid_emu.py:110-139 master-parameter loop, and any per-parameter sweep of a weight set).
@@ -280,6 +301,18 @@ FPEMU_API int fpemu_encode_multi(const void* d_table, const void* h_table, int c
 FPEMU_API int fpemu_cast_amax_scaled_noalloc(const void* in, void* out, int64_t n, int dtype, int format,
                                              int rounding, int flags, float flt_max, uint64_t seed,
                                              uint64_t elem_offset, void* stream);
+
+/* The amax-scaled sweep of a tensor list in two launches: fpemu_amax_multi, then one of these, which take the vector of
+ * maxima itself (d_amax[t], after the caller's all-reduce when the tensors are row-sharded) and derive tensor t's
+ * scale inside the cast kernel exactly as fpemu_scale_from_amax_dtype does for the table's element type
+ * (mpemu/qutils.py:283-285); tensor t's scale is stored in d_scales_out[t] (optional).  Replaces the same Python loops
+ * as fpemu_cast_multi with the per-tensor `max` scaling of mpemu/qutils.py:274-287 applied to each tensor. */
+FPEMU_API int fpemu_cast_multi_amax(const void* d_table, const void* h_table, int count, int format, int rounding,
+                                    int flags, const float* d_amax, float flt_max, float* d_scales_out, uint64_t seed,
+                                    void* stream);
+FPEMU_API int fpemu_encode_multi_amax(const void* d_table, const void* h_table, int count, int format, int rounding,
+                                      int flags, const float* d_amax, float flt_max, float* d_scales_out, uint64_t seed,
+                                      void* stream);
 
 #ifdef __cplusplus
 }

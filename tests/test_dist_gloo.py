@@ -72,10 +72,19 @@ def _worker(rank, world, port, mode, q):
         slabs = [t[r0:r1].contiguous() for t, (r0, r1) in zip(full, bounds)]
         outs, scales = fd.sharded_amax_scaled_cast(slabs, mode, row_offsets=[b[0] for b in bounds],
                                                    cols=[t.shape[1] for t in full], seed=11, kernels=OracleKernels)
+        # the pipelined schedule (runs of tensors, asynchronous all-reduce per run) must not change a bit
+        for depth in (2, 3, 8):
+            outs_p, scales_p = fd.sharded_amax_scaled_cast(slabs, mode, row_offsets=[b[0] for b in bounds],
+                                                           cols=[t.shape[1] for t in full], seed=11,
+                                                           kernels=OracleKernels, pipeline=depth)
+            assert torch.equal(scales_p, scales)
+            for a, b in zip(outs, outs_p):
+                assert torch.equal(a.view(torch.int32), b.view(torch.int32))
         plain = fd.sharded_cast(slabs, "E5M2_STOCHASTIC", row_offsets=[b[0] for b in bounds],
                                 cols=[t.shape[1] for t in full], seed=5, kernels=OracleKernels)
         codes, cscales = fd.sharded_amax_scaled_encode(slabs, mode, row_offsets=[b[0] for b in bounds],
-                                                       cols=[t.shape[1] for t in full], seed=11, kernels=OracleKernels)
+                                                       cols=[t.shape[1] for t in full], seed=11, kernels=OracleKernels,
+                                                       pipeline=2)
         assert torch.equal(cscales, scales)
         q.put((rank, [o.numpy() for o in outs], scales.numpy(), [p.numpy() for p in plain], bounds,
                [c.numpy() for c in codes]))
@@ -123,3 +132,30 @@ def test_slab_bounds_cover_all_rows_exactly_once():
                 assert a[1] == b[0]
             sizes = [b - a for a, b in cuts]
             assert max(sizes) - min(sizes) <= 1
+
+
+def test_run_splitting_and_sweep_order():
+    sys.path.insert(0, os.path.join(ROOT, "fp8-emulation-toolkit_b200"))
+    from fpemu_b200.ops import pipelined_sweep, split_runs
+    assert split_runs([10, 10, 10, 10], 2) == [(0, 2), (2, 4)]
+    assert split_runs([1, 1, 1, 100], 3) == [(0, 2), (2, 3), (3, 4)]
+    assert split_runs([5], 4) == [(0, 1)]
+    rng = np.random.default_rng(0)
+    for _ in range(500):
+        sizes = [int(v) for v in rng.choice([0, 1, 5, 100], size=rng.integers(1, 12))]
+        depth = int(rng.integers(1, 7))
+        runs = split_runs(sizes, depth)
+        assert len(runs) == min(depth, len(sizes)) and runs[0][0] == 0 and runs[-1][1] == len(sizes)
+        assert all(a[1] == b[0] for a, b in zip(runs, runs[1:])) and all(b > a for a, b in runs)
+    log = []
+
+    class Work(object):
+        def __init__(self, tag):
+            self.tag = tag
+
+        def wait(self):
+            log.append(("wait",) + self.tag)
+    pipelined_sweep([(0, 2), (2, 3)], lambda a, b: log.append(("amax", a, b)),
+                    lambda a, b: log.append(("reduce", a, b)) or Work((a, b)), lambda a, b: log.append(("apply", a, b)))
+    assert log == [("amax", 0, 2), ("reduce", 0, 2), ("amax", 2, 3), ("reduce", 2, 3),
+                   ("wait", 0, 2), ("apply", 0, 2), ("wait", 2, 3), ("apply", 2, 3)]

@@ -447,6 +447,34 @@ def test_multi_tensor_amax_scaled_cast_and_rejects_unaligned(F):
         want, ws = F.cast_amax_scaled(x, "E4M3_RNE", return_scale=True)
         assert ws.item() == s.item()
         assert_same(host(y), host(want), "amax-scaled multi")
+    # two launches per sweep (the cast kernel derives the scales): same bits as amax + scale kernel + cast with scales
+    vec = plan.amax()
+    ref_scales = F.scale_from_amax(vec, 448.0)
+    ref = [t.clone() for t in plan.cast("E4M3_RNE", d_scales=ref_scales)]
+    assert torch.equal(ref_scales, scales)
+    for y, r in zip(outs, ref):
+        assert_same(host(y), host(r), "scales derived in the cast kernel")
+    # pipelined schedule (runs of tensors, an exchange step per run) changes nothing; stochastic seeds stay per tensor
+    seen = []
+    for depth in (1, 2, 3, 7):
+        o, sc = plan.amax_scaled_cast("E4M3_STOCHASTIC", seed=77, reduce_fn=lambda v: seen.append(v.numel()), pipeline=depth)
+        got = [host(t.clone()) for t in o]
+        if depth == 1:
+            first, first_sc = got, sc.clone()
+        assert torch.equal(sc, first_sc)
+        for a, b in zip(got, first):
+            assert_same(a, b, "pipeline depth %d" % depth)
+    assert seen == [3, 2, 1, 1, 1, 1, 1, 1, 1] or seen == [3, 1, 2, 1, 1, 1, 1, 1, 1]
+    for t, x in enumerate(xs):
+        assert_same(first[t], host(F.cast(x, "E4M3_STOCHASTIC", d_scale=scales[t:t + 1], seed=77 + t)), "per-tensor seed")
+    # half tensors: the kernel-derived scale follows the half arithmetic of torch's `flt_max / vmax`
+    xh = [x.half() for x in xs]
+    ph = F.MultiTensorPlan(xh, [torch.empty_like(x) for x in xh])
+    oh, sh = ph.amax_scaled_cast("E5M2_RNE")
+    for x, y, s in zip(xh, oh, sh):
+        want, ws = F.cast_amax_scaled(x, "E5M2_RNE", return_scale=True)
+        assert ws.item() == s.item()
+        assert_same(host(y), host(want), "amax-scaled multi, half")
     with pytest.raises(ValueError):
         F.MultiTensorPlan([xs[0][1:]])                                # not 32-byte aligned
     with pytest.raises(ValueError):

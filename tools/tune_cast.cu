@@ -5,6 +5,7 @@
 #include <cstdlib>
 #include <functional>
 #include <algorithm>
+#include <string>
 #include <vector>
 
 #include "../fp8-emulation-toolkit_b200/csrc/fpemu_cast_core.cuh"
@@ -70,6 +71,81 @@ __global__ void __launch_bounds__(THREADS) k_copy(const char* in, char* out, int
 }
 
 
+// ---- TMA bulk staging experiment (north_star: "TMA bulk staging only if ncu shows it helps") ---------------------------
+// One tile of TILE bytes per CTA iteration: one elected thread issues a 1-D bulk load (cp.async.bulk, global -> shared,
+// completion on an mbarrier), all threads wait, optionally round their 32-byte vectors in place in shared memory
+// (E4M3_RNE, the same process_vec as the library kernel), then one thread issues a 1-D bulk store (shared -> global,
+// bulk async-group).  STAGES tiles are in flight per CTA (ring of buffers); several CTAs share an SM.
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t phase) {
+  asm volatile(
+      "{\n.reg .pred p;\nWAIT_LOOP:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE;\nbra WAIT_LOOP;\nDONE:\n}" :: "r"(smem_u32(bar)), "r"(phase) : "memory");
+}
+__device__ __forceinline__ void bulk_load(void* smem, const void* gmem, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               :: "r"(smem_u32(smem)), "l"(gmem), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void bulk_store(void* gmem, const void* smem, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" :: "l"(gmem), "r"(smem_u32(smem)), "r"(bytes) : "memory");
+}
+
+template <int TILE, int STAGES, bool CAST>
+__global__ void __launch_bounds__(256) k_bulk(const CastArgs a, int64_t ntiles, int tiles_per_cta) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  __shared__ uint64_t bars[STAGES];
+  const int64_t t0 = (int64_t)blockIdx.x * tiles_per_cta;
+  int64_t t1 = t0 + tiles_per_cta;
+  if (t1 > ntiles) t1 = ntiles;
+  const int my = (int)(t1 - t0);
+  const char* in = (const char*)a.in; char* out = (char*)a.out;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < STAGES; ++s) mbar_init(&bars[s], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < STAGES && s < my; ++s) {
+      mbar_expect_tx(&bars[s], TILE);
+      bulk_load(smem + s * TILE, in + (t0 + s) * TILE, TILE, &bars[s]);
+    }
+  }
+  ScaleCtx sc; sc.scale = 1.f; sc.rscale = 1.f; sc.unscale32 = false;
+  for (int i = 0; i < my; ++i) {
+    const int s = i % STAGES;
+    mbar_wait(&bars[s], (i / STAGES) & 1);
+    unsigned char* buf = smem + s * TILE;
+    if (CAST) {
+#pragma unroll
+      for (int j = 0; j < TILE / (256 * 32); ++j) {
+        Vec32* p = reinterpret_cast<Vec32*>(buf) + j * 256 + threadIdx.x;
+        Vec32 v = *p;
+        process_vec<FPEMU_FMT_E4M3, FPEMU_RND_RNE, false, FPEMU_DT_F32, false>(v, sc, a, 0);
+        *p = v;
+      }
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      bulk_store(out + (t0 + i) * TILE, buf, TILE);
+      asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      if (i + STAGES < my) {
+        asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");     // the store has read the buffer: reuse it
+        mbar_expect_tx(&bars[s], TILE);
+        bulk_load(buf, in + (t0 + i + STAGES) * TILE, TILE, &bars[s]);
+      }
+    }
+  }
+  if (threadIdx.x == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+}
+
 static float time_ms(int reps, const std::function<void()>& f) {
   cudaEvent_t a, b; CK(cudaEventCreate(&a)); CK(cudaEventCreate(&b));
   for (int i = 0; i < 3; ++i) f();
@@ -85,13 +161,29 @@ static float time_ms(int reps, const std::function<void()>& f) {
 template <int FMT, int RND, int DT, bool SCALED, int THREADS, int UNROLL>
 void run_cast(const char* name, const void* in, void* out, int64_t n, const std::vector<int>& cps) {
   CastArgs a; a.in = in; a.out = out; a.n = n; a.scale = SCALED ? 3.7f : 1.f; a.d_scale = nullptr; a.seed_lo = 1; a.seed_hi = 2;
-  a.elem_offset = 0; a.fmt = FMT; a.rnd = RND; a.flags = 0; a.d_amax = nullptr; a.flt_max = 0.f; a.d_scale_out = nullptr;
+  a.elem_offset = 0; a.fmt = FMT; a.rnd = RND; a.flags = 0; a.d_amax = nullptr; a.flt_max = 0.f; a.d_scale_out = nullptr; a.d_seed = nullptr;
   const int ve = DtInfo<DT>::kVecElems; const double bytes = 2.0 * n * DtInfo<DT>::kBytes;
   for (int c : cps) {
     int64_t want = (n / ve + THREADS * UNROLL - 1) / (THREADS * UNROLL);
     int grid = c > 0 ? (int)std::min<int64_t>(want, 148LL * c) : (int)want;
     float ms = time_ms(10, [&] { k_cast<FMT, RND, DT, SCALED, THREADS, UNROLL><<<grid, THREADS>>>(a); });
     printf("%-28s T=%4d U=%d ctas/sm=%3d grid=%8d  %8.4f ms  %7.1f GB/s\n", name, THREADS, UNROLL, c, grid, ms, bytes / ms / 1e6);
+  }
+}
+
+template <int TILE, int STAGES, bool CAST>
+void run_bulk(const char* name, const void* in, void* out, int64_t bytes_one, const std::vector<int>& tpcs) {
+  CastArgs a; a.in = in; a.out = out; a.n = bytes_one / 4; a.scale = 1.f; a.d_scale = nullptr; a.seed_lo = 1; a.seed_hi = 2;
+  a.elem_offset = 0; a.fmt = FPEMU_FMT_E4M3; a.rnd = FPEMU_RND_RNE; a.flags = 0; a.d_amax = nullptr; a.flt_max = 0.f;
+  a.d_scale_out = nullptr; a.d_seed = nullptr;
+  const int64_t ntiles = bytes_one / TILE;
+  const int smem = TILE * STAGES;
+  CK(cudaFuncSetAttribute(k_bulk<TILE, STAGES, CAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  for (int tpc : tpcs) {
+    const int64_t grid = (ntiles + tpc - 1) / tpc;
+    float ms = time_ms(10, [&] { k_bulk<TILE, STAGES, CAST><<<(unsigned)grid, 256, smem>>>(a, ntiles, tpc); });
+    printf("%-28s tile=%3d KiB stages=%d tiles/cta=%4d grid=%8lld  %8.4f ms  %7.1f GB/s\n", name, TILE / 1024, STAGES, tpc,
+           (long long)grid, ms, 2.0 * bytes_one / ms / 1e6);
   }
 }
 
@@ -137,6 +229,25 @@ int main(int argc, char** argv) {
   run_copy<512, 2, 0>("copy ld.na.256", in, out, bytes, cps);
   run_copy<256, 2, 1>("copy plain 256", in, out, bytes, cps);
   run_copy<256, 2, 2>("copy ld.nc.na.256", in, out, bytes, cps);
+  if (argc > 2 && std::string(argv[2]) == "bulk") {   // TMA bulk staging vs the plain 256-bit kernels
+    std::vector<int> one = {0};
+    for (int rep = 0; rep < 2; ++rep) {
+      run_copy<256, 2, 0>("copy ld.na.256 / st.na.256", in, out, bytes, one);
+      run_cast<FPEMU_FMT_E4M3, FPEMU_RND_RNE, FPEMU_DT_F32, false, 256, 2>("E4M3_RNE f32 (library shape)", in, out, n32, one);
+      run_bulk<16384, 1, false>("bulk copy", in, out, bytes, {1, 4});
+      run_bulk<32768, 1, false>("bulk copy", in, out, bytes, {1, 4});
+      run_bulk<16384, 2, false>("bulk copy", in, out, bytes, {2, 8, 64});
+      run_bulk<32768, 2, false>("bulk copy", in, out, bytes, {2, 8, 64});
+      run_bulk<16384, 4, false>("bulk copy", in, out, bytes, {8, 64, 885});
+      run_bulk<32768, 3, false>("bulk copy", in, out, bytes, {8, 64, 443});
+      run_bulk<16384, 1, true>("bulk E4M3_RNE f32", in, out, bytes, {1, 4});
+      run_bulk<32768, 1, true>("bulk E4M3_RNE f32", in, out, bytes, {1, 4});
+      run_bulk<16384, 2, true>("bulk E4M3_RNE f32", in, out, bytes, {2, 8, 64});
+      run_bulk<32768, 2, true>("bulk E4M3_RNE f32", in, out, bytes, {2, 8, 64});
+      run_bulk<16384, 4, true>("bulk E4M3_RNE f32", in, out, bytes, {8, 64, 885});
+    }
+    return 0;
+  }
   if (argc > 2) {   // cache-policy experiments only
     std::vector<int> one = {0};
     for (int rep = 0; rep < 3; ++rep) {
