@@ -594,7 +594,7 @@ def main():
     ap.add_argument("--e2e-elems", type=int, default=1 << 28)
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--ref-elems", type=int, default=1 << 28, help="CPU tensor size (reference arm / cpu_baseline) = the e2e size")
-    ap.add_argument("--pipeline", type=int, default=2, help="runs of tensors per C5 sweep (all-reduce overlap)")
+    ap.add_argument("--pipeline", type=int, default=1, help="runs of tensors per C5 sweep (1 measured fastest at 8 GPUs: profiles/llama7b_r2_n8.jsonl)")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")

@@ -116,7 +116,7 @@ class ShardedPlan(object):
     launch, so it executes behind the next run's amax / the previous run's cast instead of idling the GPU between
     two kernels (tools/llama7b_sweep.py measures k = 1, 2, 4)."""
 
-    def __init__(self, slabs, row_offsets=None, cols=None, outs=None, group=None, pipeline=2):
+    def __init__(self, slabs, row_offsets=None, cols=None, outs=None, group=None, pipeline=1):
         n = len(slabs)
         row_offsets = row_offsets or [0] * n
         cols = cols or [(x.shape[-1] if x.dim() > 1 else 1) for x in slabs]
