@@ -11,7 +11,9 @@
 
 namespace fpemu {
 
-template <int FMT, int RND, bool DAZ, int DT, bool SCALED>
+// ANYOFF: stochastic rounding of a slab whose elem_offset is not a multiple of 16 (the random field of a vector then
+// straddles Philox blocks); a separate instantiation so that the aligned case keeps its register count.
+template <int FMT, int RND, bool DAZ, int DT, bool SCALED, bool ANYOFF = false>
 __global__ void __launch_bounds__(kThreads) cast_vec_kernel(const CastArgs a_) {
   const CastArgs a = with_device_seed(a_);
   constexpr int VE = DtInfo<DT>::kVecElems;
@@ -34,7 +36,7 @@ __global__ void __launch_bounds__(kThreads) cast_vec_kernel(const CastArgs a_) {
   for (int j = 0; j < U; ++j) {
     const int64_t vi = base + j * kThreads;
     if (vi < nvec) {
-      process_vec<FMT, RND, DAZ, DT, SCALED>(v[j], sc, a, a.elem_offset + (uint64_t)vi * VE);
+      process_vec<FMT, RND, DAZ, DT, SCALED, ANYOFF>(v[j], sc, a, a.elem_offset + (uint64_t)vi * VE);
       stg256(out + vi * 32, v[j]);
     }
   }
@@ -52,7 +54,80 @@ __global__ void __launch_bounds__(kThreads) cast_vec_kernel(const CastArgs a_) {
       const unsigned short* p = reinterpret_cast<const unsigned short*>(a.in) + e0;
       for (int i = 0; i < tail; ++i) v.w[i >> 1] |= (uint32_t)p[i] << ((i & 1) * 16);
     }
-    process_vec<FMT, RND, DAZ, DT, SCALED>(v, sc, a, a.elem_offset + (uint64_t)e0);
+    process_vec<FMT, RND, DAZ, DT, SCALED, ANYOFF>(v, sc, a, a.elem_offset + (uint64_t)e0);
+    if (DT == FPEMU_DT_F32) {
+      uint32_t* p = reinterpret_cast<uint32_t*>(a.out) + e0;
+      for (int i = 0; i < tail; ++i) p[i] = v.w[i];
+    } else {
+      unsigned short* p = reinterpret_cast<unsigned short*>(a.out) + e0;
+      for (int i = 0; i < tail; ++i) p[i] = (unsigned short)(v.w[i >> 1] >> ((i & 1) * 16));
+    }
+  }
+}
+
+// Input and output misaligned by DIFFERENT amounts (a direct C-ABI caller casting from one view into another): vectors
+// are cut on the OUTPUT's 32-byte boundaries, so stores stay 256-bit; the matching 32 input bytes start `d` bytes into
+// an aligned 32-byte block and are assembled from the two aligned blocks they straddle (the second one is the next
+// thread's first: an L1 hit, DRAM traffic is unchanged) with a uniform funnel shift.  The upper block of the last
+// vector is read in full: it holds at least one valid byte (d > 0), so the read never leaves the buffer's last sector.
+template <int FMT, int RND, int DT, bool SCALED>
+__global__ void __launch_bounds__(kThreads) cast_shift_kernel(const CastArgs a_, const int d) {
+  const CastArgs a = with_device_seed(a_);
+  constexpr int VE = DtInfo<DT>::kVecElems;
+  constexpr int U = 2;
+  constexpr bool kAny = (RND == FPEMU_RND_STOCHASTIC);
+  const ScaleCtx sc = make_scale_ctx<DT, SCALED>(a);
+  const int64_t nvec = a.n / VE;
+  const char* in = static_cast<const char*>(a.in) - d;          // the aligned block the first vector starts in
+  char* out = static_cast<char*>(a.out);
+  const int ws = d >> 2, bs = (d & 3) * 8;
+  const int64_t base = (int64_t)blockIdx.x * (kThreads * U) + threadIdx.x;
+  Vec32 lo[U], hi[U];
+#pragma unroll
+  for (int j = 0; j < U; ++j) {
+    const int64_t vi = base + j * kThreads;
+    if (vi < nvec) {
+      lo[j] = *reinterpret_cast<const Vec32*>(in + vi * 32);     // default caching: the neighbour re-reads this block
+      hi[j] = *reinterpret_cast<const Vec32*>(in + vi * 32 + 32);
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < U; ++j) {
+    const int64_t vi = base + j * kThreads;
+    if (vi >= nvec) continue;
+    Vec32 v;
+    switch (ws) {
+#define FPEMU_SHIFT_CASE(K)                                                                              \
+      case K:                                                                                            \
+        _Pragma("unroll") for (int i = 0; i < 8; ++i) {                                                  \
+          const uint32_t x0 = (K + i < 8) ? lo[j].w[(K + i) & 7] : hi[j].w[(K + i) & 7];                 \
+          const uint32_t x1 = (K + i + 1 < 8) ? lo[j].w[(K + i + 1) & 7] : hi[j].w[(K + i + 1) & 7];     \
+          v.w[i] = __funnelshift_r(x0, x1, bs);                                                          \
+        }                                                                                                \
+        break;
+      FPEMU_SHIFT_CASE(0) FPEMU_SHIFT_CASE(1) FPEMU_SHIFT_CASE(2) FPEMU_SHIFT_CASE(3)
+      FPEMU_SHIFT_CASE(4) FPEMU_SHIFT_CASE(5) FPEMU_SHIFT_CASE(6)
+      default: FPEMU_SHIFT_CASE(7)
+#undef FPEMU_SHIFT_CASE
+    }
+    process_vec<FMT, RND, false, DT, SCALED, kAny>(v, sc, a, a.elem_offset + (uint64_t)vi * VE);
+    stg256(out + vi * 32, v);
+  }
+  // ragged tail (< one vector): element-wise loads, same register path
+  const int tail = (int)(a.n - nvec * VE);
+  if (tail > 0 && blockIdx.x == gridDim.x - 1 && threadIdx.x == 0) {
+    Vec32 v;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) v.w[i] = 0u;
+    const int64_t e0 = nvec * VE;
+    if (DT == FPEMU_DT_F32) {
+      const uint32_t* p = reinterpret_cast<const uint32_t*>(a.in) + e0;
+      for (int i = 0; i < tail; ++i) v.w[i] = p[i];
+    } else {
+      const unsigned short* p = reinterpret_cast<const unsigned short*>(a.in) + e0;
+      for (int i = 0; i < tail; ++i) v.w[i >> 1] |= (uint32_t)p[i] << ((i & 1) * 16);
+    }
+    process_vec<FMT, RND, false, DT, SCALED, kAny>(v, sc, a, a.elem_offset + (uint64_t)e0);
     if (DT == FPEMU_DT_F32) {
       uint32_t* p = reinterpret_cast<uint32_t*>(a.out) + e0;
       for (int i = 0; i < tail; ++i) p[i] = v.w[i];
@@ -171,39 +246,42 @@ __global__ void __launch_bounds__(kThreads) cast_vec_generic_kernel(const CastAr
 typedef void (*CastKernel)(const CastArgs);
 
 template <int FMT, int RND, bool DAZ, int DT>
-static CastKernel pick_scaled(bool scaled) {
-  if (FMT == FPEMU_FMT_BF16 || FMT == FPEMU_FMT_FP16) return cast_vec_kernel<FMT, RND, DAZ, DT, false>;
+static CastKernel pick_scaled(bool scaled, bool anyoff) {
+  constexpr bool kSR = (RND == FPEMU_RND_STOCHASTIC);
+  if (FMT == FPEMU_FMT_BF16 || FMT == FPEMU_FMT_FP16)
+    return (kSR && anyoff) ? cast_vec_kernel<FMT, RND, DAZ, DT, false, kSR> : cast_vec_kernel<FMT, RND, DAZ, DT, false>;
+  if (kSR && anyoff) return scaled ? cast_vec_kernel<FMT, RND, DAZ, DT, true, kSR> : cast_vec_kernel<FMT, RND, DAZ, DT, false, kSR>;
   return scaled ? cast_vec_kernel<FMT, RND, DAZ, DT, true> : cast_vec_kernel<FMT, RND, DAZ, DT, false>;
 }
 
 template <int FMT, int RND, bool DAZ>
-static CastKernel pick_dt(int dt, bool scaled) {
+static CastKernel pick_dt(int dt, bool scaled, bool anyoff) {
   switch (dt) {
-    case FPEMU_DT_F32:  return pick_scaled<FMT, RND, DAZ, FPEMU_DT_F32>(scaled);
-    case FPEMU_DT_F16:  return pick_scaled<FMT, RND, DAZ, FPEMU_DT_F16>(scaled);
-    default:            return pick_scaled<FMT, RND, DAZ, FPEMU_DT_BF16>(scaled);
+    case FPEMU_DT_F32:  return pick_scaled<FMT, RND, DAZ, FPEMU_DT_F32>(scaled, anyoff);
+    case FPEMU_DT_F16:  return pick_scaled<FMT, RND, DAZ, FPEMU_DT_F16>(scaled, anyoff);
+    default:            return pick_scaled<FMT, RND, DAZ, FPEMU_DT_BF16>(scaled, anyoff);
   }
 }
 
 template <int FMT>
-static CastKernel pick_rnd(int rnd, bool daz, int dt, bool scaled) {
+static CastKernel pick_rnd(int rnd, bool daz, int dt, bool scaled, bool anyoff) {
   if (FMT == FPEMU_FMT_E5M2 && daz) {
-    if (rnd == FPEMU_RND_RNE) return pick_dt<FPEMU_FMT_E5M2, FPEMU_RND_RNE, true>(dt, scaled);
-    if (rnd == FPEMU_RND_STOCHASTIC) return pick_dt<FPEMU_FMT_E5M2, FPEMU_RND_STOCHASTIC, true>(dt, scaled);
-    if (rnd == FPEMU_RND_RNAZ) return pick_dt<FPEMU_FMT_E5M2, FPEMU_RND_RNAZ, true>(dt, scaled);
-    if (rnd == FPEMU_RND_RNTZ) return pick_dt<FPEMU_FMT_E5M2, FPEMU_RND_RNTZ, true>(dt, scaled);
+    if (rnd == FPEMU_RND_RNE) return pick_dt<FPEMU_FMT_E5M2, FPEMU_RND_RNE, true>(dt, scaled, anyoff);
+    if (rnd == FPEMU_RND_STOCHASTIC) return pick_dt<FPEMU_FMT_E5M2, FPEMU_RND_STOCHASTIC, true>(dt, scaled, anyoff);
+    if (rnd == FPEMU_RND_RNAZ) return pick_dt<FPEMU_FMT_E5M2, FPEMU_RND_RNAZ, true>(dt, scaled, anyoff);
+    if (rnd == FPEMU_RND_RNTZ) return pick_dt<FPEMU_FMT_E5M2, FPEMU_RND_RNTZ, true>(dt, scaled, anyoff);
     return nullptr;
   }
   if (FMT == FPEMU_FMT_E5M2) {                    // the reference's extra E5M2 rounding modes (:1058-1158)
-    if (rnd == FPEMU_RND_RNAZ) return pick_dt<FPEMU_FMT_E5M2, FPEMU_RND_RNAZ, false>(dt, scaled);
-    if (rnd == FPEMU_RND_RNTZ) return pick_dt<FPEMU_FMT_E5M2, FPEMU_RND_RNTZ, false>(dt, scaled);
-    if (rnd == FPEMU_RND_RPINF) return pick_dt<FPEMU_FMT_E5M2, FPEMU_RND_RPINF, false>(dt, scaled);
-    if (rnd == FPEMU_RND_RNINF) return pick_dt<FPEMU_FMT_E5M2, FPEMU_RND_RNINF, false>(dt, scaled);
+    if (rnd == FPEMU_RND_RNAZ) return pick_dt<FPEMU_FMT_E5M2, FPEMU_RND_RNAZ, false>(dt, scaled, anyoff);
+    if (rnd == FPEMU_RND_RNTZ) return pick_dt<FPEMU_FMT_E5M2, FPEMU_RND_RNTZ, false>(dt, scaled, anyoff);
+    if (rnd == FPEMU_RND_RPINF) return pick_dt<FPEMU_FMT_E5M2, FPEMU_RND_RPINF, false>(dt, scaled, anyoff);
+    if (rnd == FPEMU_RND_RNINF) return pick_dt<FPEMU_FMT_E5M2, FPEMU_RND_RNINF, false>(dt, scaled, anyoff);
   }
   switch (rnd) {
-    case FPEMU_RND_RNE:        return pick_dt<FMT, FPEMU_RND_RNE, false>(dt, scaled);
-    case FPEMU_RND_RTZ:        return (FMT == FPEMU_FMT_FP16) ? nullptr : pick_dt<FMT, FPEMU_RND_RTZ, false>(dt, scaled);
-    case FPEMU_RND_STOCHASTIC: return pick_dt<FMT, FPEMU_RND_STOCHASTIC, false>(dt, scaled);
+    case FPEMU_RND_RNE:        return pick_dt<FMT, FPEMU_RND_RNE, false>(dt, scaled, anyoff);
+    case FPEMU_RND_RTZ:        return (FMT == FPEMU_FMT_FP16) ? nullptr : pick_dt<FMT, FPEMU_RND_RTZ, false>(dt, scaled, anyoff);
+    case FPEMU_RND_STOCHASTIC: return pick_dt<FMT, FPEMU_RND_STOCHASTIC, false>(dt, scaled, anyoff);
     default:                   return nullptr;
   }
 }
@@ -224,15 +302,51 @@ static CastKernel pick_generic(int fmt, int rnd, int dt) {
   return pick_generic_dt<-1, -1>(dt);
 }
 
-static CastKernel pick_kernel(int fmt, int rnd, bool daz, int dt, bool scaled) {
+static CastKernel pick_kernel(int fmt, int rnd, bool daz, int dt, bool scaled, bool anyoff) {
   switch (fmt) {
-    case FPEMU_FMT_E5M2: return pick_rnd<FPEMU_FMT_E5M2>(rnd, daz, dt, scaled);
-    case FPEMU_FMT_E4M3: return pick_rnd<FPEMU_FMT_E4M3>(rnd, daz, dt, scaled);
-    case FPEMU_FMT_E3M4: return pick_rnd<FPEMU_FMT_E3M4>(rnd, daz, dt, scaled);
-    case FPEMU_FMT_BF16: return pick_rnd<FPEMU_FMT_BF16>(rnd, false, dt, false);
-    case FPEMU_FMT_FP16: return pick_rnd<FPEMU_FMT_FP16>(rnd, false, dt, false);
-    case FPEMU_FMT_E4M3_IEEE: return daz ? nullptr : pick_rnd<FPEMU_FMT_E4M3_IEEE>(rnd, false, dt, scaled);
+    case FPEMU_FMT_E5M2: return pick_rnd<FPEMU_FMT_E5M2>(rnd, daz, dt, scaled, anyoff);
+    case FPEMU_FMT_E4M3: return pick_rnd<FPEMU_FMT_E4M3>(rnd, daz, dt, scaled, anyoff);
+    case FPEMU_FMT_E3M4: return pick_rnd<FPEMU_FMT_E3M4>(rnd, daz, dt, scaled, anyoff);
+    case FPEMU_FMT_BF16: return pick_rnd<FPEMU_FMT_BF16>(rnd, false, dt, false, anyoff);
+    case FPEMU_FMT_FP16: return pick_rnd<FPEMU_FMT_FP16>(rnd, false, dt, false, anyoff);
+    case FPEMU_FMT_E4M3_IEEE: return daz ? nullptr : pick_rnd<FPEMU_FMT_E4M3_IEEE>(rnd, false, dt, scaled, anyoff);
     default:             return nullptr;   // FP4 and anything without a packed kernel: generic kernel
+  }
+}
+
+// cast_shift_kernel instances: the four north_star formats x {RNE, STOCHASTIC, RTZ}; other modes keep the element-wise
+// kernel for this layout.
+typedef void (*ShiftKernel)(const CastArgs, const int);
+
+template <int FMT, int RND>
+static ShiftKernel shift_dt(int dt, bool scaled) {
+  constexpr bool kTakesScale = (FMT != FPEMU_FMT_BF16);
+  switch (dt) {
+    case FPEMU_DT_F32:
+      return (kTakesScale && scaled) ? cast_shift_kernel<FMT, RND, FPEMU_DT_F32, kTakesScale> : cast_shift_kernel<FMT, RND, FPEMU_DT_F32, false>;
+    case FPEMU_DT_F16:
+      return (kTakesScale && scaled) ? cast_shift_kernel<FMT, RND, FPEMU_DT_F16, kTakesScale> : cast_shift_kernel<FMT, RND, FPEMU_DT_F16, false>;
+    default:
+      return (kTakesScale && scaled) ? cast_shift_kernel<FMT, RND, FPEMU_DT_BF16, kTakesScale> : cast_shift_kernel<FMT, RND, FPEMU_DT_BF16, false>;
+  }
+}
+template <int FMT>
+static ShiftKernel shift_rnd(int rnd, int dt, bool scaled) {
+  switch (rnd) {
+    case FPEMU_RND_RNE:        return shift_dt<FMT, FPEMU_RND_RNE>(dt, scaled);
+    case FPEMU_RND_RTZ:        return shift_dt<FMT, FPEMU_RND_RTZ>(dt, scaled);
+    case FPEMU_RND_STOCHASTIC: return shift_dt<FMT, FPEMU_RND_STOCHASTIC>(dt, scaled);
+    default:                   return nullptr;
+  }
+}
+static ShiftKernel pick_shift(int fmt, int rnd, bool daz, int dt, bool scaled) {
+  if (daz) return nullptr;
+  switch (fmt) {
+    case FPEMU_FMT_E5M2: return shift_rnd<FPEMU_FMT_E5M2>(rnd, dt, scaled);
+    case FPEMU_FMT_E4M3: return shift_rnd<FPEMU_FMT_E4M3>(rnd, dt, scaled);
+    case FPEMU_FMT_E3M4: return shift_rnd<FPEMU_FMT_E3M4>(rnd, dt, scaled);
+    case FPEMU_FMT_BF16: return shift_rnd<FPEMU_FMT_BF16>(rnd, dt, false);
+    default:             return nullptr;
   }
 }
 
@@ -253,18 +367,19 @@ int launch_cast(const CastArgs& a, int dtype, cudaStream_t stream) {
   const bool scaled = (a.d_scale != nullptr) || (a.d_amax != nullptr) || (a.scale != 1.0f);
   const bool daz = (a.flags & FPEMU_FLAG_DAZ) != 0;
   const bool aligned = (((uintptr_t)a.in | (uintptr_t)a.out) & 31u) == 0;
+  // the packed kernels gather their random fields per element index (any elem_offset); only the element-wise rounding
+  // inside cast_vec_generic_kernel still assumes that a vector does not straddle Philox blocks
   const bool rng_ok = (a.rnd != FPEMU_RND_STOCHASTIC) || ((a.elem_offset & 15u) == 0);
-  CastKernel k = (aligned && rng_ok) ? pick_kernel(a.fmt, a.rnd, daz, dtype, scaled) : nullptr;
+  CastKernel k = aligned ? pick_kernel(a.fmt, a.rnd, daz, dtype, scaled, !rng_ok) : nullptr;
   const int sms = device_info().sm_count;
   // A view that starts off a 32-byte boundary (a slice of a flat parameter buffer, x[1:]), input and output off by the
   // same amount: the few elements up to the boundary go through the element-wise kernel, the rest is an aligned
-  // problem for the vector kernels — provided the random stream lines up there too.
+  // problem for the vector kernels.
   const uintptr_t mis = (uintptr_t)a.in & 31u;
   if (!aligned && mis == ((uintptr_t)a.out & 31u)) {
     const int esz = dtype_bytes(dtype);
     const int64_t head = (int64_t)((32u - mis) / (uintptr_t)esz);
-    const bool body_rng_ok = (a.rnd != FPEMU_RND_STOCHASTIC) || (((a.elem_offset + (uint64_t)head) & 15u) == 0);
-    if (head < a.n && body_rng_ok && pick_kernel(a.fmt, a.rnd, daz, dtype, scaled) != nullptr) {
+    if (head < a.n && pick_kernel(a.fmt, a.rnd, daz, dtype, scaled, false) != nullptr) {
       CastArgs h = a;
       h.n = head;
       cast_generic_kernel<<<1, 32, 0, stream>>>(h, dtype);
@@ -274,6 +389,33 @@ int launch_cast(const CastArgs& a, int dtype, cudaStream_t stream) {
       b.n = a.n - head;
       b.elem_offset = a.elem_offset + (uint64_t)head;
       return launch_cast(b, dtype, stream);
+    }
+  }
+  // Input and output off a 32-byte boundary by different amounts: element-wise head up to the OUTPUT's boundary, then
+  // cast_shift_kernel (aligned 256-bit stores, input assembled from two aligned blocks).
+  if (!aligned && mis != ((uintptr_t)a.out & 31u)) {
+    ShiftKernel sk = pick_shift(a.fmt, a.rnd, daz, dtype, scaled);
+    const int esz = dtype_bytes(dtype);
+    const uintptr_t mis_out = (uintptr_t)a.out & 31u;
+    const int64_t head = mis_out ? (int64_t)((32u - mis_out) / (uintptr_t)esz) : 0;
+    if (sk != nullptr && head < a.n) {
+      if (head > 0) {
+        CastArgs h = a;
+        h.n = head;
+        cast_generic_kernel<<<1, 32, 0, stream>>>(h, dtype);
+      }
+      CastArgs b = a;
+      b.in = static_cast<const char*>(a.in) + head * esz;
+      b.out = static_cast<char*>(a.out) + head * esz;
+      b.n = a.n - head;
+      b.elem_offset = a.elem_offset + (uint64_t)head;
+      const int d = (int)((uintptr_t)b.in & 31u);                // != 0: the two buffers are misaligned differently
+      const int ve = dtype == FPEMU_DT_F32 ? 8 : 16;
+      int64_t want = (b.n / ve + kThreads * 2 - 1) / (kThreads * 2);
+      if (want < 1) want = 1;
+      if (want > 0x7FFFFFFFLL) return FPEMU_ERR_TOO_LARGE;
+      sk<<<(unsigned)want, kThreads, 0, stream>>>(b, d);
+      return (int)cudaGetLastError();
     }
   }
   if (k != nullptr) {

@@ -62,7 +62,7 @@ __device__ __forceinline__ void put_pair(Vec32& v, int k, float2 f) {
 // 16 random bits per element: element g uses 16-bit lane (g % 8) of Philox(g / 8), i.e. pair k of the vector
 // uses word ((2k) % 8) / 2 of call (2k) / 8.
 template <int RND, int DT>
-__device__ __forceinline__ void process_vec_bf16(Vec32& v, const CastArgs& a, uint64_t g0, const uint4& r0, const uint4& r1) {
+__device__ __forceinline__ void process_vec_bf16(Vec32& v, const CastArgs& a, uint64_t g0, const uint32_t (&rl)[8]) {
   constexpr int kPairs = DtInfo<DT>::kVecElems / 2;
   constexpr bool kSR = (RND == FPEMU_RND_STOCHASTIC);
   const Vec32 orig = v;
@@ -70,9 +70,7 @@ __device__ __forceinline__ void process_vec_bf16(Vec32& v, const CastArgs& a, ui
   uint32_t packed[kPairs];
 #pragma unroll
   for (int k = 0; k < kPairs; ++k) {
-    const uint4& rr = (k < 4) ? r0 : r1;
-    const int wsel = k & 3;
-    const uint32_t rbits = kSR ? (wsel == 0 ? rr.x : (wsel == 1 ? rr.y : (wsel == 2 ? rr.z : rr.w))) : 0u;
+    const uint32_t rbits = kSR ? rl[k] : 0u;
     const float2 f = get_pair<DT>(v, k);
     packed[k] = round_pair_bf16<RND>(f.x, f.y, rbits, nan_any);
   }
@@ -83,9 +81,7 @@ __device__ __forceinline__ void process_vec_bf16(Vec32& v, const CastArgs& a, ui
     // rare: redo the vector element by element with the reference's integer rule (keeps NaN payload high bits)
 #pragma unroll
     for (int k = 0; k < kPairs; ++k) {
-      const uint4& rr = (k < 4) ? r0 : r1;
-      const int wsel = k & 3;
-      const uint32_t rbits = kSR ? (wsel == 0 ? rr.x : (wsel == 1 ? rr.y : (wsel == 2 ? rr.z : rr.w))) : 0u;
+      const uint32_t rbits = kSR ? rl[k] : 0u;
       float2 f = get_pair<DT>(orig, k);
       f.x = __uint_as_float(round_one_bf16(__float_as_uint(f.x), RND, rbits & 0xFFFFu));
       f.y = __uint_as_float(round_one_bf16(__float_as_uint(f.y), RND, rbits >> 16));
@@ -114,19 +110,70 @@ __device__ __forceinline__ ScaleCtx make_scale_ctx(const CastArgs& a) {
   return sc;
 }
 
+// Bytes [shift, shift + 16) of the 32-byte string Philox(block) | Philox(block + 1): the random field of a vector that
+// does not start on a Philox-block boundary (a slab of a sharded tensor whose first global element index is not a
+// multiple of 16).  Only the ANYOFF kernel variants contain this code: its two draws and the select chains cost
+// 20-odd registers, which the aligned case should not pay for.
+__device__ __forceinline__ uint4 rand_window16(uint32_t seed_lo, uint32_t seed_hi, uint64_t block, uint32_t shift) {
+  const uint4 r0 = philox4x32_10(seed_lo, seed_hi, block);
+  const uint4 r1 = philox4x32_10(seed_lo, seed_hi, block + 1);
+  const uint32_t w[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
+  const uint32_t ws = shift >> 2, bs = (shift & 3u) * 8u;        // shift < 16: ws in 0..3
+  uint32_t o[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const uint32_t lo = ws == 0 ? w[i] : ws == 1 ? w[i + 1] : ws == 2 ? w[i + 2] : w[i + 3];
+    const uint32_t hi = ws == 0 ? w[i + 1] : ws == 1 ? w[i + 2] : ws == 2 ? w[i + 3] : w[i + 4];
+    o[i] = __funnelshift_r(lo, hi, bs);
+  }
+  return make_uint4(o[0], o[1], o[2], o[3]);
+}
+
 // Random bytes of one vector for the 8-bit formats: element g uses byte (g % 16) of Philox(g / 16).
-template <int FMT, int RND, int DT>
+// ANYOFF = false: g0 is a multiple of the vector length and of 8 (the launch guarantees elem_offset % 16 == 0);
+// ANYOFF = true : any g0.
+template <int FMT, int RND, int DT, bool ANYOFF = false>
 __device__ __forceinline__ void vec_rand_bytes(const CastArgs& a, uint64_t g0, uint32_t (&rw)[4]) {
   rw[0] = rw[1] = rw[2] = rw[3] = 0u;
   if (RND == FPEMU_RND_STOCHASTIC) {
-    const uint4 r = philox4x32_10(a.seed_lo, a.seed_hi, g0 >> 4);
     const uint32_t m = (FMT == FPEMU_FMT_E5M2) ? 0xFFFFFFFFu
                      : ((FMT == FPEMU_FMT_E4M3 || FMT == FPEMU_FMT_E4M3_IEEE) ? 0x7F7F7F7Fu : 0x3F3F3F3Fu);
-    if (DT == FPEMU_DT_F32) {                       // 8 elements: half of the 16-byte draw
-      const bool hi = (g0 >> 3) & 1u;
-      rw[0] = (hi ? r.z : r.x) & m; rw[1] = (hi ? r.w : r.y) & m;
+    if (ANYOFF) {
+      const uint4 r = rand_window16(a.seed_lo, a.seed_hi, g0 >> 4, (uint32_t)g0 & 15u);
+      rw[0] = r.x & m; rw[1] = r.y & m;
+      if (DT != FPEMU_DT_F32) { rw[2] = r.z & m; rw[3] = r.w & m; }
     } else {
-      rw[0] = r.x & m; rw[1] = r.y & m; rw[2] = r.z & m; rw[3] = r.w & m;
+      const uint4 r = philox4x32_10(a.seed_lo, a.seed_hi, g0 >> 4);
+      if (DT == FPEMU_DT_F32) {                       // 8 elements: half of the 16-byte draw
+        const bool hi = (g0 >> 3) & 1u;
+        rw[0] = (hi ? r.z : r.x) & m; rw[1] = (hi ? r.w : r.y) & m;
+      } else {
+        rw[0] = r.x & m; rw[1] = r.y & m; rw[2] = r.z & m; rw[3] = r.w & m;
+      }
+    }
+  }
+}
+
+// 16-bit random lanes of one vector for the BFLOAT16 / FLOAT16 targets: element g uses lane (g % 8) of Philox(g / 8);
+// word k of `rl` holds the lanes of elements g0 + 2k (low half) and g0 + 2k + 1 (high half).
+template <int DT, bool ANYOFF = false>
+__device__ __forceinline__ void vec_rand_lanes(const CastArgs& a, uint64_t g0, uint32_t (&rl)[8]) {
+  constexpr int NW = DtInfo<DT>::kVecElems / 2;                 // 4 words (fp32 tensors) or 8 (16-bit tensors)
+  rl[4] = rl[5] = rl[6] = rl[7] = 0u;
+  if (!ANYOFF) {
+    const uint4 r0 = philox4x32_10(a.seed_lo, a.seed_hi, g0 >> 3);
+    rl[0] = r0.x; rl[1] = r0.y; rl[2] = r0.z; rl[3] = r0.w;
+    if (NW > 4) {
+      const uint4 r1 = philox4x32_10(a.seed_lo, a.seed_hi, (g0 >> 3) + 1);
+      rl[4] = r1.x; rl[5] = r1.y; rl[6] = r1.z; rl[7] = r1.w;
+    }
+  } else {
+    const uint32_t sh = 2u * ((uint32_t)g0 & 7u);
+    const uint4 r0 = rand_window16(a.seed_lo, a.seed_hi, g0 >> 3, sh);
+    rl[0] = r0.x; rl[1] = r0.y; rl[2] = r0.z; rl[3] = r0.w;
+    if (NW > 4) {
+      const uint4 r1 = rand_window16(a.seed_lo, a.seed_hi, (g0 >> 3) + 1, sh);
+      rl[4] = r1.x; rl[5] = r1.y; rl[6] = r1.z; rl[7] = r1.w;
     }
   }
 }
@@ -164,15 +211,16 @@ __device__ __forceinline__ void finish_pair(Vec32& v, int k, uint32_t q, const S
   }
 }
 
-// One 32-byte vector whose first element has global index g0 (a multiple of the vector length).
-template <int FMT, int RND, bool DAZ, int DT, bool SCALED>
+// One 32-byte vector whose first element has global index g0: a multiple of the vector length on a launch whose
+// elem_offset is a multiple of 16, or any value in the ANYOFF instantiations.
+template <int FMT, int RND, bool DAZ, int DT, bool SCALED, bool ANYOFF = false>
 __device__ __forceinline__ void process_vec(Vec32& v, const ScaleCtx& sc, const CastArgs& a, uint64_t g0) {
   constexpr int kPairs = DtInfo<DT>::kVecElems / 2;
   constexpr bool kSR = (RND == FPEMU_RND_STOCHASTIC);
 
   if (FMT == FPEMU_FMT_E5M2 || FMT == FPEMU_FMT_E4M3 || FMT == FPEMU_FMT_E3M4 || FMT == FPEMU_FMT_E4M3_IEEE) {
     uint32_t rw[4];
-    vec_rand_bytes<FMT, RND, DT>(a, g0, rw);
+    vec_rand_bytes<FMT, RND, DT, ANYOFF>(a, g0, rw);
 #pragma unroll
     for (int k = 0; k < kPairs; ++k) {
       const uint32_t h = pair_to_h<DT, SCALED>(v, k, sc);
@@ -190,11 +238,8 @@ __device__ __forceinline__ void process_vec(Vec32& v, const ScaleCtx& sc, const 
       v.w[k] &= ~tiny;
     }
   } else if (FMT == FPEMU_FMT_BF16) {
-    uint4 r0 = make_uint4(0u, 0u, 0u, 0u), r1 = r0;
-    if (kSR) {
-      r0 = philox4x32_10(a.seed_lo, a.seed_hi, g0 >> 3);
-      if (kPairs > 4) r1 = philox4x32_10(a.seed_lo, a.seed_hi, (g0 >> 3) + 1);
-    }
+    uint32_t rl[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
+    if (kSR) vec_rand_lanes<DT, ANYOFF>(a, g0, rl);
     if (kSR && DT == FPEMU_DT_F16) {
       // fp16 tensor, stochastic BFLOAT16: for fp16-normal values only the 3 lowest fp16 mantissa bits are dropped and
       // only the top 3 of the 16 random bits can carry into the kept part ((m3 << 13) + r16 >= 2^16  <=>  m3 + (r16 >> 13)
@@ -205,9 +250,7 @@ __device__ __forceinline__ void process_vec(Vec32& v, const ScaleCtx& sc, const 
       uint32_t special = 0u, q[kPairs];
 #pragma unroll
       for (int k = 0; k < kPairs; ++k) {
-        const uint4& rr = (k < 4) ? r0 : r1;
-        const int wsel = k & 3;
-        const uint32_t rbits = wsel == 0 ? rr.x : (wsel == 1 ? rr.y : (wsel == 2 ? rr.z : rr.w));
+        const uint32_t rbits = rl[k];
         const uint32_t h = v.w[k];
         const __half2 av = as_h2(h & kAbs2);
         const uint32_t nrm = __hge2_mask(av, as_h2(h2c(0x0400)));          // normal or Inf (false for NaN)
@@ -222,15 +265,12 @@ __device__ __forceinline__ void process_vec(Vec32& v, const ScaleCtx& sc, const 
         return;
       }
     }
-    process_vec_bf16<RND, DT>(v, a, g0, r0, r1);
+    process_vec_bf16<RND, DT>(v, a, g0, rl);
   } else {
     // FLOAT16 target: per element; 13 random bits per element from the same 16-bit lanes as BFLOAT16
     const bool daz = (a.flags & FPEMU_FLAG_DAZ) != 0;
-    uint4 r0 = make_uint4(0u, 0u, 0u, 0u), r1 = r0;
-    if (kSR) {
-      r0 = philox4x32_10(a.seed_lo, a.seed_hi, g0 >> 3);
-      if (kPairs > 4) r1 = philox4x32_10(a.seed_lo, a.seed_hi, (g0 >> 3) + 1);
-    }
+    uint32_t rl[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
+    if (kSR) vec_rand_lanes<DT, ANYOFF>(a, g0, rl);
     if (kSR && DT != FPEMU_DT_F16) {
       // Stochastic FLOAT16 of fp32 / bf16 values (fpemu_kernels.cu:340-372): inside the fp16 normal range
       // [2^-14, 2^16) the reference adds 13 random bits under the kept mantissa and truncates — done here on the fp32
@@ -241,9 +281,7 @@ __device__ __forceinline__ void process_vec(Vec32& v, const ScaleCtx& sc, const 
       uint32_t nan_any = 0u, hp[kPairs];
 #pragma unroll
       for (int k = 0; k < kPairs; ++k) {
-        const uint4& rr = (k < 4) ? r0 : r1;
-        const int wsel = k & 3;
-        const uint32_t rbits = wsel == 0 ? rr.x : (wsel == 1 ? rr.y : (wsel == 2 ? rr.z : rr.w));
+        const uint32_t rbits = rl[k];
         const float2 f = get_pair<DT>(v, k);
         uint32_t u0 = __float_as_uint(f.x), u1 = __float_as_uint(f.y);
         if (((u0 & 0x7FFFFFFFu) - 0x38800000u) < 0x0F000000u) u0 = (u0 + (rbits & 0x1FFFu)) & 0xFFFFE000u;
@@ -259,9 +297,7 @@ __device__ __forceinline__ void process_vec(Vec32& v, const ScaleCtx& sc, const 
     }
 #pragma unroll
     for (int k = 0; k < kPairs; ++k) {
-      const uint4& rr = (k < 4) ? r0 : r1;
-      const int wsel = k & 3;
-      const uint32_t rbits = kSR ? (wsel == 0 ? rr.x : (wsel == 1 ? rr.y : (wsel == 2 ? rr.z : rr.w))) : 0u;
+      const uint32_t rbits = kSR ? rl[k] : 0u;
       float2 f = get_pair<DT>(v, k);
       const bool ih = (DT == FPEMU_DT_F16);
       f.x = __half2float(__ushort_as_half((unsigned short)round_one_fp16(f.x, RND, daz, ih, rbits & 0xFFFFu)));

@@ -22,7 +22,7 @@ struct MtEntry {
 };
 struct MtHeader {
   int32_t count;
-  int32_t dtype;
+  int32_t dtype;          // element type in the low byte; bit 8 (kMtAnyOffset): some elem_offset is not a multiple of 16
   uint32_t total_cast;
   uint32_t total_amax;
 };
@@ -30,6 +30,7 @@ static_assert(sizeof(MtEntry) == 40, "table layout");
 static_assert(sizeof(MtHeader) == 16, "table layout");
 
 constexpr int kMtAmaxUnroll = 4;
+constexpr int kMtAnyOffset = 0x100;
 
 __device__ __forceinline__ const MtEntry* mt_entries(const void* table) {
   return reinterpret_cast<const MtEntry*>(static_cast<const char*>(table) + sizeof(MtHeader));
@@ -64,7 +65,7 @@ __device__ __forceinline__ float mt_scale(const CastArgs& proto, const float* d_
   return s;
 }
 
-template <int FMT, int RND, int DT, bool SCALED>
+template <int FMT, int RND, int DT, bool SCALED, bool ANYOFF = false>
 __global__ void __launch_bounds__(kThreads) cast_multi_kernel(const void* table, const int count, const CastArgs proto,
                                                              const float* d_scales) {
   constexpr int VE = DtInfo<DT>::kVecElems;
@@ -99,7 +100,7 @@ __global__ void __launch_bounds__(kThreads) cast_multi_kernel(const void* table,
   for (int j = 0; j < U; ++j) {
     const int64_t vi = base + j * kThreads;
     if (vi < nvec) {
-      process_vec<FMT, RND, false, DT, SCALED>(v[j], sc, a, a.elem_offset + (uint64_t)vi * VE);
+      process_vec<FMT, RND, false, DT, SCALED, ANYOFF>(v[j], sc, a, a.elem_offset + (uint64_t)vi * VE);
       stg256(out + vi * 32, v[j]);
     }
   }
@@ -118,7 +119,7 @@ __global__ void __launch_bounds__(kThreads) cast_multi_kernel(const void* table,
       const unsigned short* p = reinterpret_cast<const unsigned short*>(a.in) + e0;
       for (int i = 0; i < tail; ++i) w.w[i >> 1] |= (uint32_t)p[i] << ((i & 1) * 16);
     }
-    process_vec<FMT, RND, false, DT, SCALED>(w, sc, a, a.elem_offset + (uint64_t)e0);
+    process_vec<FMT, RND, false, DT, SCALED, ANYOFF>(w, sc, a, a.elem_offset + (uint64_t)e0);
     if (DT == FPEMU_DT_F32) {
       uint32_t* p = reinterpret_cast<uint32_t*>(a.out) + e0;
       for (int i = 0; i < tail; ++i) p[i] = w.w[i];
@@ -194,24 +195,27 @@ __global__ void __launch_bounds__(kThreads) amax_multi_kernel(const void* table,
 typedef void (*MultiCastKernel)(const void*, const int, const CastArgs, const float*);
 
 template <int FMT, int RND, int DT>
-static MultiCastKernel mpick_scaled(bool scaled) {
-  if (FMT == FPEMU_FMT_BF16 || FMT == FPEMU_FMT_FP16) return cast_multi_kernel<FMT, RND, DT, false>;
+static MultiCastKernel mpick_scaled(bool scaled, bool anyoff) {
+  constexpr bool kSR = (RND == FPEMU_RND_STOCHASTIC);
+  if (FMT == FPEMU_FMT_BF16 || FMT == FPEMU_FMT_FP16)
+    return (kSR && anyoff) ? cast_multi_kernel<FMT, RND, DT, false, kSR> : cast_multi_kernel<FMT, RND, DT, false>;
+  if (kSR && anyoff) return scaled ? cast_multi_kernel<FMT, RND, DT, true, kSR> : cast_multi_kernel<FMT, RND, DT, false, kSR>;
   return scaled ? cast_multi_kernel<FMT, RND, DT, true> : cast_multi_kernel<FMT, RND, DT, false>;
 }
 template <int FMT, int RND>
-static MultiCastKernel mpick_dt(int dt, bool scaled) {
+static MultiCastKernel mpick_dt(int dt, bool scaled, bool anyoff) {
   switch (dt) {
-    case FPEMU_DT_F32:  return mpick_scaled<FMT, RND, FPEMU_DT_F32>(scaled);
-    case FPEMU_DT_F16:  return mpick_scaled<FMT, RND, FPEMU_DT_F16>(scaled);
-    default:            return mpick_scaled<FMT, RND, FPEMU_DT_BF16>(scaled);
+    case FPEMU_DT_F32:  return mpick_scaled<FMT, RND, FPEMU_DT_F32>(scaled, anyoff);
+    case FPEMU_DT_F16:  return mpick_scaled<FMT, RND, FPEMU_DT_F16>(scaled, anyoff);
+    default:            return mpick_scaled<FMT, RND, FPEMU_DT_BF16>(scaled, anyoff);
   }
 }
 template <int FMT>
-static MultiCastKernel mpick_rnd(int rnd, int dt, bool scaled) {
+static MultiCastKernel mpick_rnd(int rnd, int dt, bool scaled, bool anyoff) {
   switch (rnd) {
-    case FPEMU_RND_RNE:        return mpick_dt<FMT, FPEMU_RND_RNE>(dt, scaled);
-    case FPEMU_RND_RTZ:        return (FMT == FPEMU_FMT_FP16) ? nullptr : mpick_dt<FMT, FPEMU_RND_RTZ>(dt, scaled);
-    case FPEMU_RND_STOCHASTIC: return mpick_dt<FMT, FPEMU_RND_STOCHASTIC>(dt, scaled);
+    case FPEMU_RND_RNE:        return mpick_dt<FMT, FPEMU_RND_RNE>(dt, scaled, anyoff);
+    case FPEMU_RND_RTZ:        return (FMT == FPEMU_FMT_FP16) ? nullptr : mpick_dt<FMT, FPEMU_RND_RTZ>(dt, scaled, anyoff);
+    case FPEMU_RND_STOCHASTIC: return mpick_dt<FMT, FPEMU_RND_STOCHASTIC>(dt, scaled, anyoff);
     default:                   return nullptr;
   }
 }
@@ -251,12 +255,14 @@ extern "C" int fpemu_multi_table_build(const fpemu_tensor_desc* descs, int count
   MtHeader* h = static_cast<MtHeader*>(h_table);
   MtEntry* e = reinterpret_cast<MtEntry*>(static_cast<char*>(h_table) + sizeof(MtHeader));
   uint64_t cast_ctas = 0, amax_ctas = 0;
+  bool any_offset = false;
   for (int t = 0; t < count; ++t) {
     const fpemu_tensor_desc& d = descs[t];
     if (d.n < 0 || (d.n > 0 && (d.in == nullptr || d.out == nullptr))) return FPEMU_ERR_ARG;
-    // the multi-tensor kernels only have the vector path: 32-byte aligned buffers, Philox-group aligned offsets
-    if ((((uintptr_t)d.in | (uintptr_t)d.out) & 31u) != 0 || (d.elem_offset & 15u) != 0) return FPEMU_ERR_ALIGN;
+    // the multi-tensor kernels only have the vector path: 32-byte aligned buffers (any element offset)
+    if ((((uintptr_t)d.in | (uintptr_t)d.out) & 31u) != 0) return FPEMU_ERR_ALIGN;
     e[t].in = d.in; e[t].out = d.out; e[t].n = d.n; e[t].elem_offset = d.elem_offset;
+    any_offset = any_offset || (d.elem_offset & 15u) != 0;
     e[t].cta_cast = (uint32_t)cast_ctas;
     e[t].cta_amax = (uint32_t)amax_ctas;
     const int64_t nvec = d.n / ve;
@@ -268,7 +274,7 @@ extern "C" int fpemu_multi_table_build(const fpemu_tensor_desc* descs, int count
     amax_ctas += (uint64_t)m;
     if (cast_ctas > 0x7FFFFFFFull || amax_ctas > 0x7FFFFFFFull) return FPEMU_ERR_TOO_LARGE;
   }
-  h->count = count; h->dtype = dtype; h->total_cast = (uint32_t)cast_ctas; h->total_amax = (uint32_t)amax_ctas;
+  h->count = count; h->dtype = dtype | (any_offset ? kMtAnyOffset : 0); h->total_cast = (uint32_t)cast_ctas; h->total_amax = (uint32_t)amax_ctas;
   return FPEMU_OK;
 }
 
@@ -278,7 +284,7 @@ extern "C" int fpemu_amax_multi(const void* d_table, const void* h_table, int co
   if (h->count != count) return FPEMU_ERR_ARG;
   if (h->total_amax == 0) return FPEMU_OK;
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-  switch (h->dtype) {
+  switch (h->dtype & 0xFF) {
     case FPEMU_DT_F32:  amax_multi_kernel<FPEMU_DT_F32><<<h->total_amax, kThreads, 0, stream>>>(d_table, count, d_amax); break;
     case FPEMU_DT_F16:  amax_multi_kernel<FPEMU_DT_F16><<<h->total_amax, kThreads, 0, stream>>>(d_table, count, d_amax); break;
     default:            amax_multi_kernel<FPEMU_DT_BF16><<<h->total_amax, kThreads, 0, stream>>>(d_table, count, d_amax); break;
@@ -301,20 +307,23 @@ int launch_multi(bool codes, const void* d_table, const void* h_table, int count
   if (d_amax != nullptr && !takes_scale) return FPEMU_ERR_MODE;
   const bool scaled = (d_scales != nullptr || d_amax != nullptr) && takes_scale;
   MultiCastKernel k = nullptr;
+  const int dt = h->dtype & 0xFF;
+  const bool anyoff = (h->dtype & kMtAnyOffset) != 0 && rounding == FPEMU_RND_STOCHASTIC;
+  if (codes && anyoff) return FPEMU_ERR_ALIGN;                   // the code kernels draw per aligned vector only
   if (codes) {
     switch (format) {
-      case FPEMU_FMT_E5M2: k = epick_rnd<FPEMU_FMT_E5M2>(rounding, h->dtype, scaled); break;
-      case FPEMU_FMT_E4M3: k = epick_rnd<FPEMU_FMT_E4M3>(rounding, h->dtype, scaled); break;
-      case FPEMU_FMT_E3M4: k = epick_rnd<FPEMU_FMT_E3M4>(rounding, h->dtype, scaled); break;
+      case FPEMU_FMT_E5M2: k = epick_rnd<FPEMU_FMT_E5M2>(rounding, dt, scaled); break;
+      case FPEMU_FMT_E4M3: k = epick_rnd<FPEMU_FMT_E4M3>(rounding, dt, scaled); break;
+      case FPEMU_FMT_E3M4: k = epick_rnd<FPEMU_FMT_E3M4>(rounding, dt, scaled); break;
       default: break;                                            // only the three 8-bit formats have codes
     }
   } else {
     switch (format) {
-      case FPEMU_FMT_E5M2: k = mpick_rnd<FPEMU_FMT_E5M2>(rounding, h->dtype, scaled); break;
-      case FPEMU_FMT_E4M3: k = mpick_rnd<FPEMU_FMT_E4M3>(rounding, h->dtype, scaled); break;
-      case FPEMU_FMT_E3M4: k = mpick_rnd<FPEMU_FMT_E3M4>(rounding, h->dtype, scaled); break;
-      case FPEMU_FMT_BF16: k = mpick_rnd<FPEMU_FMT_BF16>(rounding, h->dtype, false); break;
-      case FPEMU_FMT_FP16: k = mpick_rnd<FPEMU_FMT_FP16>(rounding, h->dtype, false); break;
+      case FPEMU_FMT_E5M2: k = mpick_rnd<FPEMU_FMT_E5M2>(rounding, dt, scaled, anyoff); break;
+      case FPEMU_FMT_E4M3: k = mpick_rnd<FPEMU_FMT_E4M3>(rounding, dt, scaled, anyoff); break;
+      case FPEMU_FMT_E3M4: k = mpick_rnd<FPEMU_FMT_E3M4>(rounding, dt, scaled, anyoff); break;
+      case FPEMU_FMT_BF16: k = mpick_rnd<FPEMU_FMT_BF16>(rounding, dt, false, anyoff); break;
+      case FPEMU_FMT_FP16: k = mpick_rnd<FPEMU_FMT_FP16>(rounding, dt, false, anyoff); break;
       default: break;
     }
   }

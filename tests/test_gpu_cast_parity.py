@@ -477,8 +477,19 @@ def test_multi_tensor_amax_scaled_cast_and_rejects_unaligned(F):
         assert_same(host(y), host(want), "amax-scaled multi, half")
     with pytest.raises(ValueError):
         F.MultiTensorPlan([xs[0][1:]])                                # not 32-byte aligned
+    # element offsets that are not on a Philox-block boundary (slabs of a sharded tensor with an odd row length):
+    # the list launch draws the straddled blocks (ANYOFF kernel instance), same bits as the per-tensor casts
+    offs = [8, 3, 1 << 33 | 5]
+    for dt in (torch.float32, torch.bfloat16):
+        xo = [x.to(dt) for x in xs]
+        po = F.MultiTensorPlan(xo, [torch.empty_like(x) for x in xo], elem_offsets=offs)
+        for mode in ("E4M3_STOCHASTIC", "BFLOAT16_STOCHASTIC", "E5M2_RNE"):
+            outs_o = po.cast(mode, seed=31)
+            for t, (x, y) in enumerate(zip(xo, outs_o)):
+                assert_same(host(y), host(F.cast(x, mode, seed=31 + t, elem_offset=offs[t])), "%s odd offset %d" % (mode, t))
     with pytest.raises(ValueError):
-        F.MultiTensorPlan([xs[0]], elem_offsets=[8])                  # not a Philox-group boundary
+        F.MultiTensorPlan(xs, [torch.empty(x.shape, dtype=torch.uint8, device="cuda") for x in xs],
+                          elem_offsets=offs).encode("E4M3_STOCHASTIC")      # code kernels: aligned offsets only
 
 
 # ------------------------------------------------------------------------------------------ out-of-bounds guard

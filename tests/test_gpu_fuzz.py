@@ -101,3 +101,26 @@ def test_random_encode_decode_configurations(F, chunk):
         back = F.decode(codes, fmt, dtype=xt.dtype, scale=c["scale"])
         back_np = back.view(torch.int16).cpu().numpy().view(np.uint16) if xt.dtype == torch.bfloat16 else back.cpu().numpy()
         assert_same(bits32(back_np, c["dt"]), bits32(O.decode(want, fmt, dtype=np_dt, scale=c["scale"]), c["dt"]), str(c))
+
+
+@pytest.mark.parametrize("chunk", range(4))
+def test_input_and_output_misaligned_by_different_amounts(F, chunk):
+    """A caller-supplied output whose offset from a 32-byte boundary differs from the input's (cast_shift_kernel: aligned
+    stores, input assembled from two aligned blocks), any element offset, guard zones around the output."""
+    rng = np.random.default_rng(3000 + chunk)
+    modes = ["E5M2_RNE", "E5M2_STOCHASTIC", "E5M2_RTZ", "E4M3_RNE", "E4M3_STOCHASTIC", "E4M3_RTZ", "E3M4_RNE",
+             "E3M4_STOCHASTIC", "BFLOAT16_RNE", "BFLOAT16_STOCHASTIC", "BFLOAT16_RTZ", "E4M3_IEEE_RNE", "FLOAT16_STOCHASTIC"]
+    for _ in range(40):
+        c = random_config(rng, modes)
+        in_off, out_off = int(rng.integers(0, 16)), int(rng.integers(0, 16))
+        xn, xt = as_dtype(wide(c["n"] + in_off, c["data_seed"]), c["dt"])
+        xn, xt = xn[in_off:], xt[in_off:]
+        guard = 40
+        big = torch.full((guard + out_off + c["n"] + guard,), 77.0, dtype=xt.dtype, device="cuda")
+        out = big[guard + out_off: guard + out_off + c["n"]]
+        want = O.cast(xn, c["mode"], scale=c["scale"], seed=c["seed"], elem_offset=c["elem_off"])
+        F.cast(xt, c["mode"], out=out, scale=c["scale"], seed=c["seed"], elem_offset=c["elem_off"])
+        got_np = out.view(torch.int16).cpu().numpy().view(np.uint16) if xt.dtype == torch.bfloat16 else out.cpu().numpy()
+        what = "%s in_off=%d out_off=%d" % (c, in_off, out_off)
+        assert_same(bits32(got_np, c["dt"]), bits32(want, c["dt"]), what)
+        assert bool((big[:guard + out_off] == 77.0).all()) and bool((big[guard + out_off + c["n"]:] == 77.0).all()), what

@@ -56,6 +56,7 @@ def main():
     ap.add_argument("--quick", action="store_true")
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "sweep.json"))
     ap.add_argument("--reps", type=int, default=20)
+    ap.add_argument("--odd", action="store_true", help="only the odd-layout rows (misaligned views, odd element offsets)")
     args = ap.parse_args()
     sizes = [20, 24, 28, 30] if args.quick else [20, 22, 24, 26, 28, 30, 31, 32]
     rows = []
@@ -64,6 +65,40 @@ def main():
         peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
     except Exception:
         pass
+
+    if args.odd:
+        # odd layouts only: slabs whose element offset is not a multiple of 16 (stochastic), views off a 32-byte
+        # boundary with input and output off by the same / by different amounts, a tensor list with odd offsets
+        n = 1 << 28
+        for dname, dtype in (("fp32", torch.float32), ("bf16", torch.bfloat16)):
+            esz = torch.empty(0, dtype=dtype).element_size()
+            x = torch.randn(n + 64, device="cuda").to(dtype)
+            y = torch.empty(n + 64, dtype=dtype, device="cuda")
+            cases = [("aligned, elem_offset 0", 0, 0, 0), ("aligned, elem_offset 3", 0, 0, 3), ("aligned, elem_offset 8", 0, 0, 8),
+                     ("in and out off by 1 element", 1, 1, 0), ("in off by 1, out aligned", 1, 0, 0),
+                     ("in aligned, out off by 3", 0, 3, 0), ("in off by 5, out off by 2, elem_offset 3", 5, 2, 3)]
+            for mode in ("E4M3_RNE", "E4M3_STOCHASTIC", "BFLOAT16_STOCHASTIC"):
+                for label, io, oo, eo in cases:
+                    xi, yo = x[io:io + n], y[oo:oo + n]
+                    ms = time_launches(lambda i: F.cast(xi, mode, out=yo, seed=7, elem_offset=eo), 1, args.reps)
+                    rows.append({"impl": "b200", "mode": mode, "dtype": dname, "log2n": 28, "layout": label, "ms": ms,
+                                 "GB/s": 2.0 * n * esz / (ms * 1e-3) / 1e9})
+            parts = [x[k * (n // 8):(k + 1) * (n // 8)] for k in range(8)]
+            outs = [y[k * (n // 8):(k + 1) * (n // 8)] for k in range(8)]
+            for label, offs in (("list of 8 slabs, offsets multiple of 16", [16 * k for k in range(8)]),
+                                ("list of 8 slabs, odd offsets", [16 * k + 3 for k in range(8)])):
+                plan = F.MultiTensorPlan(parts, outs, elem_offsets=offs)
+                ms = time_launches(lambda i: plan.cast("E4M3_STOCHASTIC", seed=7), 1, args.reps)
+                rows.append({"impl": "b200", "mode": "E4M3_STOCHASTIC (fpemu_cast_multi)", "dtype": dname, "log2n": 28,
+                             "layout": label, "ms": ms, "GB/s": 2.0 * n * esz / (ms * 1e-3) / 1e9})
+            del x, y, parts, outs
+            torch.cuda.empty_cache()
+        os.makedirs(os.path.dirname(args.out), exist_ok=True)
+        with open(args.out, "w") as f:
+            json.dump({"gpu": torch.cuda.get_device_name(0), "peak_measured_GBs": peak, "rows": rows}, f, indent=0)
+        for r in rows:
+            print("%-36s %-5s %-44s %8.1f GB/s" % (r["mode"], r["dtype"], r["layout"], r["GB/s"]))
+        return
 
     # ---- ours
     for dname, dtype in DTYPES.items():
