@@ -63,6 +63,92 @@ __global__ void scale_from_amax_kernel(const float* d_amax, int count, float flt
   if (i < count) d_scale[i] = scale_from_amax(d_amax[i], flt_max, true, dt);
 }
 
+// ------------------------------------------------------------------------------------------ mean scaling
+// Per-tensor `mean` scaling of quantize_tensor (mpemu/qutils.py:276-281):
+//     mean = torch.mean(abs(x));  mean = abs(mean) if abs(mean) > 1e-5 else flt_min
+//     scale = flt_min / abs(mean)  (a 0-dim tensor: reciprocal * flt_min);  scale = 1.0 if scale < 1.0 else scale
+// Two launches, deterministic: per-CTA partial sums of |x| in double (fixed grid-stride assignment) into scratch,
+// then one CTA adds the partials in a fixed tree order and applies the rule.  The sum is exact to well below one
+// float ulp of the mean, so the result equals torch's float reduction except where that reduction's own rounding
+// decides — which only matters when mean < flt_min (otherwise the scale is 1 exactly).
+constexpr int kMeanParts = 1024;
+
+template <int DT>
+__global__ void __launch_bounds__(256) abs_sum_partial_kernel(const void* in_, int64_t n, double* parts) {
+  constexpr int VE = DtInfo<DT>::kVecElems;
+  const char* in = static_cast<const char*>(in_);
+  const int64_t nvec = n / VE;
+  double acc = 0.0;
+  for (int64_t vi = (int64_t)blockIdx.x * 256 + threadIdx.x; vi < nvec; vi += (int64_t)gridDim.x * 256) {
+    const Vec32 v = ldg256(in + vi * 32);
+    float s = 0.0f;                                            // 8 / 16 addends in float, then into the double
+#pragma unroll
+    for (int k = 0; k < VE / 2; ++k) {
+      const float2 f = get_pair<DT>(v, k);
+      s += fabsf(f.x) + fabsf(f.y);
+    }
+    acc += (double)s;
+  }
+  if (blockIdx.x == 0)
+    for (int64_t i = nvec * VE + threadIdx.x; i < n; i += 256) acc += (double)fabsf(load_elem(in_, i, DT));
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xFFFFFFFFu, acc, o);
+  __shared__ double warp_sum[8];
+  if ((threadIdx.x & 31) == 0) warp_sum[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0.0;
+    for (int w = 0; w < 8; ++w) t += warp_sum[w];
+    parts[blockIdx.x] = t;
+  }
+}
+
+__global__ void __launch_bounds__(256) abs_sum_generic_kernel(const void* in, int64_t n, int dt, double* parts) {
+  double acc = 0.0;
+  for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (int64_t)gridDim.x * 256)
+    acc += (double)fabsf(load_elem(in, i, dt));
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xFFFFFFFFu, acc, o);
+  __shared__ double warp_sum[8];
+  if ((threadIdx.x & 31) == 0) warp_sum[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0.0;
+    for (int w = 0; w < 8; ++w) t += warp_sum[w];
+    parts[blockIdx.x] = t;
+  }
+}
+
+__global__ void __launch_bounds__(kMeanParts) mean_scale_kernel(const double* parts, int nparts, int64_t n, float flt_min,
+                                                              float floor_, int dt, float* d_scale) {
+  __shared__ double s[kMeanParts];
+  s[threadIdx.x] = threadIdx.x < nparts ? parts[threadIdx.x] : 0.0;
+  __syncthreads();
+  for (int o = kMeanParts / 2; o > 0; o >>= 1) {
+    if (threadIdx.x < o) s[threadIdx.x] += s[threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    float mean = (float)(s[0] / (double)n);
+    if (dt == FPEMU_DT_F16) mean = __half2float(__float2half_rn(mean));           // torch.mean of a half tensor is a half
+    float scale = 1.0f;                                       // below the floor `mean` becomes flt_min: flt_min / flt_min
+    if (fabsf(mean) > floor_) {
+      if (dt == FPEMU_DT_F16) {
+        const float r = __half2float(__float2half_rn(__frcp_rn(fabsf(mean))));
+        scale = __half2float(__float2half_rn(r * flt_min));
+      } else {                                                // float32, and bfloat16 (not dispatched upstream) widened
+        scale = __fmul_rn(__frcp_rn(fabsf(mean)), flt_min);
+      }
+    }
+    if (scale < 1.0f) scale = 1.0f;
+    *d_scale = scale;
+  }
+}
+
+// Power-of-two block scale for ONE block spanning the whole tensor (block_size == size: the reference CPU op's reading,
+// cpp/fpemu_impl.cpp:778-779), derived on the device from the reduced maximum.
+__global__ void block_scale_from_amax_kernel(const float* d_amax, int fmt, int dt, float* d_scale) {
+  *d_scale = block_scale(*d_amax, fmt, dt);
+}
+
 // ------------------------------------------------------------------------------------------ blocked
 // Fast path: a quantization block is `vpb` (power of two, <= 32) consecutive 32-byte vectors, i.e. it lives in
 // `vpb` adjacent lanes of one warp: xor-shuffle butterfly, everything stays in registers (8 B/elem fp32).
@@ -326,6 +412,44 @@ extern "C" int fpemu_scale_from_amax_dtype(const float* d_amax, int count, float
 
 extern "C" int fpemu_scale_from_amax(const float* d_amax, int count, float flt_max, float* d_scale, void* stream_) {
   return fpemu_scale_from_amax_dtype(d_amax, count, flt_max, FPEMU_DT_F32, d_scale, stream_);
+}
+
+extern "C" int fpemu_mean_scale_work_bytes(void) { return (int)(kMeanParts * sizeof(double)); }
+
+extern "C" int fpemu_scale_from_abs_mean(const void* in, int64_t n, int dtype, float flt_min, float mean_floor,
+                                         void* d_work, float* d_scale, void* stream_) {
+  if (n <= 0 || in == nullptr || d_work == nullptr || d_scale == nullptr) return FPEMU_ERR_ARG;
+  if (dtype < 0 || dtype >= FPEMU_DT_COUNT) return FPEMU_ERR_DTYPE;
+  if (((uintptr_t)in % (uintptr_t)dtype_bytes(dtype)) || ((uintptr_t)d_work % 8u)) return FPEMU_ERR_ALIGN;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  double* parts = static_cast<double*>(d_work);
+  const int ve = dtype == FPEMU_DT_F32 ? 8 : 16;
+  int64_t want = (n / ve + 256 * 4 - 1) / (256 * 4);
+  if (want < 1) want = 1;
+  const int grid = (int)(want < kMeanParts ? want : kMeanParts);
+  if (((uintptr_t)in & 31u) == 0) {
+    switch (dtype) {
+      case FPEMU_DT_F32:  abs_sum_partial_kernel<FPEMU_DT_F32><<<grid, 256, 0, stream>>>(in, n, parts); break;
+      case FPEMU_DT_F16:  abs_sum_partial_kernel<FPEMU_DT_F16><<<grid, 256, 0, stream>>>(in, n, parts); break;
+      default:            abs_sum_partial_kernel<FPEMU_DT_BF16><<<grid, 256, 0, stream>>>(in, n, parts); break;
+    }
+  } else {
+    abs_sum_generic_kernel<<<grid, 256, 0, stream>>>(in, n, dtype, parts);
+  }
+  cudaError_t err = cudaGetLastError();
+  if (err != cudaSuccess) return (int)err;
+  mean_scale_kernel<<<1, kMeanParts, 0, stream>>>(parts, grid, n, flt_min, mean_floor, dtype, d_scale);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int fpemu_block_scale_from_amax(const float* d_amax, int format, int dtype, float* d_scale, void* stream_) {
+  if (d_amax == nullptr || d_scale == nullptr) return FPEMU_ERR_ARG;
+  if (dtype < 0 || dtype >= FPEMU_DT_COUNT) return FPEMU_ERR_DTYPE;
+  if (format != FPEMU_FMT_E5M2 && format != FPEMU_FMT_E4M3 && format != FPEMU_FMT_E3M4 && format != FPEMU_FMT_E4M3_IEEE &&
+      format != FPEMU_FMT_FP4)
+    return FPEMU_ERR_MODE;
+  block_scale_from_amax_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream_)>>>(d_amax, format, dtype, d_scale);
+  return (int)cudaGetLastError();
 }
 
 extern "C" int fpemu_cast_blocked(const void* in, void* out, int64_t n, int64_t block_size, int dtype, int format,

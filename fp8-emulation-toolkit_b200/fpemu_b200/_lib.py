@@ -36,6 +36,9 @@ SIGNATURES = {
     "fpemu_cast_amax_scaled_noalloc": (_i32, [_vp, _vp, _i64, _i32, _i32, _i32, _i32, _f32, _u64, _u64, _vp]),
     "fpemu_cast_host": (_i32, [_vp, _vp, _i64, _i32, _i32, _i32, _i32, _f32, _u64, _vp, _vp, _i64, _vp, _vp, _vp]),
     "fpemu_cast_host_multi": (_i32, [_vp, _i64, _i32, _vp, _i32, _vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp]),
+    "fpemu_mean_scale_work_bytes": (_i32, []),
+    "fpemu_scale_from_abs_mean": (_i32, [_vp, _i64, _i32, _f32, _f32, _vp, _vp, _vp]),
+    "fpemu_block_scale_from_amax": (_i32, [_vp, _i32, _i32, _vp, _vp]),
     "fpemu_fused_work_floats": (_i32, []),
     "fpemu_cast_amax_scaled_fused": (_i32, [_vp, _vp, _i64, _i32, _i32, _i32, _i32, _f32, _vp, _i32, _u64, _u64, _vp]),
     "fpemu_cast_rows_scaled": (_i32, [_vp, _vp, _i64, _i64, _i32, _i32, _i32, _i32, _vp, _u64, _u64, _vp]),

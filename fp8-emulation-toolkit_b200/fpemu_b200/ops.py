@@ -229,17 +229,12 @@ def cast_blocked(x, mode, block_size, out=None, seed=None, elem_offset=0, n=None
         # one block = the whole (large) tensor (the reference CPU op's reading of block_size == size,
         # cpp/fpemu_impl.cpp:778-779): amax kernel, then the power-of-two block scale derived on the device from
         # the exponent field of the maximum (fpemu_kernels.cu:409-413, 577-581, 909-911), then the plain cast
-        a = amax(x, n=n)
-        p2 = (a.view(torch.int32) & 0x7F800000).view(torch.float32)
-        d_scale = 2.0 * p2
-        if fmt == L.FMT_E5M2:
-            if x.dtype == torch.float16:                     # `scalar_t scale` is a half in that instantiation
-                d_scale = (d_scale.half() / 16384.0).float()
-            else:
-                d_scale = d_scale / 16384.0
-        elif fmt in (L.FMT_E4M3, L.FMT_E4M3_IEEE):
-            d_scale = d_scale / 8.0
-        return cast(x, mode, out=out, d_scale=d_scale.contiguous(), seed=seed, elem_offset=elem_offset, n=n,
+        work = torch.zeros(2, dtype=torch.float32, device=x.device)
+        amax(x, out=work[0:1], n=n)
+        with _on_device(x):
+            st = L.lib().fpemu_block_scale_from_amax(work.data_ptr(), fmt, _dt(x), work.data_ptr() + 4, _stream(x))
+        L.check(st, "fpemu_block_scale_from_amax")
+        return cast(x, mode, out=out, d_scale=work[1:2], seed=seed, elem_offset=elem_offset, n=n,
                     unscale_fp32=unscale_fp32)
     with _on_device(x):
         st = L.lib().fpemu_cast_blocked(x.data_ptr(), out.data_ptr(), n, int(block_size), _dt(x), fmt, rnd, flags,
@@ -270,6 +265,21 @@ def scale_from_amax(d_amax, flt_max, out=None, dtype=torch.float32):
         st = L.lib().fpemu_scale_from_amax_dtype(d_amax.data_ptr(), d_amax.numel(), float(flt_max), _DT[dtype],
                                                  out.data_ptr(), _stream(d_amax))
     L.check(st, "fpemu_scale_from_amax")
+    return out
+
+
+def mean_scale(x, flt_min, mean_floor=1e-5, out=None):
+    """Per-tensor `mean` scale of quantize_tensor (qutils.py:276-281) as a 1-element float32 CUDA tensor:
+    max(1, flt_min / mean|x|) with the reference's floor on the mean; two launches, no host sync."""
+    _check_tensor(x)
+    if out is None:
+        out = torch.empty(1, dtype=torch.float32, device=x.device)
+    stream = _stream(x)
+    work = _work_for(x, stream)                       # >= 8 KiB, 512-byte aligned: room for the partial sums
+    with _on_device(x):
+        st = L.lib().fpemu_scale_from_abs_mean(x.data_ptr(), x.numel(), _dt(x), float(flt_min), float(mean_floor),
+                                               work.data_ptr() + 8, out.data_ptr(), stream)
+    L.check(st, "fpemu_scale_from_abs_mean")
     return out
 
 

@@ -127,8 +127,11 @@ class ModuleQuantConfig(object):
     def register_weight_grad_hook(self, module):
         """Weight-gradient tensor hook (reference :173-189): in-place cast."""
         def quantize_weight_grad(grad):
-            if self.wtgrad_qconfig is not None and self.wtgrad_qconfig.is_enabled:
-                grad.data = quantize_tensor(grad.data, self.wtgrad_qconfig, None, inplace=True)
+            qc = self.wtgrad_qconfig
+            if qc is not None and qc.is_enabled:
+                if _GRADS.defer(module, qc, grad):
+                    return grad              # cast in place, with every other deferred gradient, when this backward ends
+                grad.data = quantize_tensor(grad.data, qc, None, inplace=True)
             return grad
         if type(module) in (torch.nn.Conv2d, torch.nn.Linear):
             if module.weight is not None and module.weight.requires_grad:
@@ -266,10 +269,13 @@ def quantize_tensor(tensor, qtconfig, qtparams, inplace=False):
         if qtconfig.scaling_method == "mean":
             # same expression as the reference (:276-281), kept on the device: no .item(), no host sync
             flt_min = qtconfig.get_flt_min()
-            mean = torch.abs(torch.mean(torch.abs(tensor.detach().flatten())))
-            mean = torch.where(mean > 1e-5, mean, torch.full_like(mean, flt_min))
-            scale = torch.clamp(flt_min / mean, min=1.0)
-            return fpemu_device_fn(tensor, mode, inplace=inplace, scale=scale.float().reshape(1))
+            if takes_scale and _supported_dtype(tensor) and tensor.is_contiguous() and tensor.numel() > 0:
+                scale = _F.mean_scale(tensor.detach(), flt_min, 1e-5)        # two small kernels, deterministic
+            else:
+                mean = torch.abs(torch.mean(torch.abs(tensor.detach().flatten())))
+                mean = torch.where(mean > 1e-5, mean, torch.full_like(mean, flt_min))
+                scale = torch.clamp(flt_min / mean, min=1.0).float().reshape(1)
+            return fpemu_device_fn(tensor, mode, inplace=inplace, scale=scale)
         if takes_scale and _supported_dtype(tensor):
             return _scaled_cast(tensor, mode, inplace, "tensor", flt_max, 0, 0, True)
         return fpemu_device_fn(tensor, mode, inplace=inplace)
@@ -352,8 +358,12 @@ def get_quantization_parameters(tensor, qtconfig):
 
 
 def quantize_weights_of_a_module(module, wt_qconfig, name=""):
-    """Reference: mpemu/qutils.py:458-468."""
-    module.weight.data.copy_(quantize_tensor(module.weight.data, wt_qconfig, None))
+    """Reference: mpemu/qutils.py:458-468 (cast into a new tensor, then copy back): same values from ONE in-place pass."""
+    w = module.weight.data
+    if w.is_cuda and w.is_contiguous():
+        quantize_tensor(w, wt_qconfig, None, inplace=True)
+    else:
+        w.copy_(quantize_tensor(w, wt_qconfig, None))
 
 
 def quantize_model_weights(model, model_qconfig_dict):
@@ -363,12 +373,138 @@ def quantize_model_weights(model, model_qconfig_dict):
             quantize_weights_of_a_module(module, model_qconfig_dict[name].wt_qconfig, name=name)
 
 
+# ------------------------------------------------------------------------------------------ batched launches
+# The reference casts tensor by tensor from Python.  Two groups of those casts do not depend on anything computed
+# during the step and are issued here as ONE multi-tensor sweep each (fpemu_amax_multi + fpemu_cast_multi_amax /
+# fpemu_cast_multi) instead of one launch per module:
+#   * the weights of all hooked modules of a model in training (re-quantized in place every forward,
+#     qutils.py:520-522): cast when the ROOT module's forward starts; each module's own pre-forward hook then finds
+#     its weight done.  Same values as the per-module casts (weights do not change during a forward).
+#   * the weight gradients (tensor hooks, qutils.py:173-189): a hook whose parameter has no accumulated gradient yet
+#     leaves the incoming gradient untouched; when the backward pass ends, the `.grad` tensors of all such parameters
+#     are cast in place in one launch.  With a gradient already accumulated (micro-batching) the hook casts at once,
+#     as the reference does, because cast(a) + cast(b) != cast(a + b).
+# Calling a hooked module on its own (no root forward) or set_batched_hooks(False) gives the per-tensor behaviour.
+_BATCH_HOOKS = True
+
+
+def set_batched_hooks(flag):
+    global _BATCH_HOOKS
+    _BATCH_HOOKS = bool(flag)
+
+
+def _plan_for(cache, tensors):
+    key = tuple((t.data_ptr(), t.numel()) for t in tensors)
+    plan = cache.get(key)
+    if plan is None:
+        if len(cache) > 16:
+            cache.clear()
+        try:
+            plan = _F.MultiTensorPlan(tensors)
+        except ValueError:
+            plan = False                                    # unaligned storage: per-tensor casts
+        cache[key] = plan
+    return plan
+
+
+def _batchable(qc, t):
+    return (qc is not None and qc.is_enabled and not qc.per_channel and not qc.fine_grained and t is not None
+            and t.is_cuda and t.is_contiguous() and _supported_dtype(t) and t.numel() > 0
+            and (qc.scaling is not True or qc.scaling_method == "max") and "int" not in qc.dtype)
+
+
+def _cast_list(plans, tensors, qc):
+    """In-place cast of a list of same-dtype tensors that share one TensorQuantConfig: one sweep, or False."""
+    plan = _plan_for(plans, tensors)
+    if plan is False:
+        return False
+    mode = qc.mode_string()
+    if qc.scaling is True and _L.parse_mode(mode)[0] not in (_L.FMT_BF16, _L.FMT_FP16):
+        plan.amax_scaled_cast(mode, flt_max=qc.get_flt_max(), unscale_fp32=_UNSCALE_FP32)
+    else:
+        plan.cast(mode, unscale_fp32=_UNSCALE_FP32)
+    return True
+
+
+class _WeightBatch(object):
+    """Forward-pre hook of the ROOT module of a model in training: one sweep over the weights of all hooked modules."""
+
+    def __init__(self, modules):
+        self.modules = modules
+        self.plans = {}
+        self.active = False            # True only while the root module's forward is running
+        self.gen = 0
+
+    def done(self, root, inputs, output):
+        self.active = False
+
+    def __call__(self, root, inputs):
+        self.active = False
+        if not _BATCH_HOOKS or torch.cuda.is_current_stream_capturing():
+            return None
+        self.active = True
+        self.gen += 1
+        groups = {}
+        for m in self.modules:
+            qc = m.qconfig.wt_qconfig
+            w = getattr(m, "weight", None)
+            if w is None or not _batchable(qc, w.data) or qc.dtype in ["bfloat16"]:
+                continue
+            groups.setdefault((qc.mode_string(), qc.scaling, w.dtype, w.device), (qc, []))[1].append(m)
+        for qc, mods in groups.values():
+            if len(mods) > 1 and _cast_list(self.plans, [m.weight.data for m in mods], qc):
+                for m in mods:
+                    m._fpemu_weight_done = (self, self.gen)
+        return None
+
+
+class _GradBatch(object):
+    """Weight gradients whose cast was deferred to the end of the running backward pass."""
+
+    def __init__(self):
+        self.pending = []
+        self.plans = {}
+
+    def defer(self, module, qc, grad):
+        if not _BATCH_HOOKS or module.weight.grad is not None or not _batchable(qc, grad) \
+                or torch.cuda.is_current_stream_capturing():
+            return False
+        # one callback per deferred gradient: the first one to run casts everything, the others find nothing to do
+        # (a single callback per pass would be lost for good if a backward pass raised before running it)
+        torch.autograd.Variable._execution_engine.queue_callback(self.flush)
+        self.pending.append((module, qc))
+        return True
+
+    def flush(self):
+        pending, self.pending = self.pending, []
+        groups, seen = {}, set()
+        for m, qc in pending:
+            g = m.weight.grad
+            if g is None or id(m) in seen:
+                continue
+            seen.add(id(m))
+            if not g.is_contiguous():
+                g.data = quantize_tensor(g.data, qc, None, inplace=True)
+                continue
+            groups.setdefault((qc.mode_string(), g.dtype, g.device), (qc, []))[1].append(g.data)
+        for qc, grads in groups.values():
+            if not _cast_list(self.plans, grads, qc):
+                for g in grads:
+                    quantize_tensor(g, qc, None, inplace=True)
+
+
+_GRADS = _GradBatch()
+
+
 def quantize_module_weights_and_inputs(self, input):
     """Forward-pre hook (reference :478-549): weights in place, inputs out of place."""
     qc = self.qconfig
     if qc.wt_qconfig is not None and qc.wt_qconfig.dtype in ["bfloat16"]:
         qc.weight_master = self.weight.data.clone()
-    if qc.wt_qconfig is not None and qc.wt_qconfig.is_enabled:
+    done = getattr(self, "_fpemu_weight_done", None)
+    if done is not None and done[0].active and done[0].gen == done[1]:
+        self._fpemu_weight_done = None                       # cast by the root module's sweep at the start of this forward
+    elif qc.wt_qconfig is not None and qc.wt_qconfig.is_enabled:
         self.weight.data = quantize_tensor(self.weight.data, qc.wt_qconfig, self.qparams.wt_qparams, inplace=True)
     if qc.iact_qconfig is not None and qc.iact_qconfig.is_enabled:
         input = tuple(quantize_tensor(t, qc.iact_qconfig, None, inplace=False) if torch.is_tensor(t) and
@@ -426,6 +562,12 @@ def add_quantization_hooks(model, model_qconfig_dict, is_training=False):
                 if module.qconfig.igrad_qconfig is not None:
                     handles.append(module.register_full_backward_hook(quantize_module_gradient))
                 module.qconfig.register_weight_grad_hook(module)
+    if is_training:
+        hooked = [m for name, m in model.named_modules() if name in model_qconfig_dict and hasattr(m, "weight")]
+        if len(hooked) > 1:
+            batch = _WeightBatch(hooked)
+            handles.append(model.register_forward_pre_hook(batch, prepend=True))
+            handles.append(model.register_forward_hook(batch.done, always_call=True))
     return handles
 
 

@@ -151,6 +151,20 @@ FPEMU_API int fpemu_scale_from_amax(const float* d_amax, int count, float flt_ma
 FPEMU_API int fpemu_scale_from_amax_dtype(const float* d_amax, int count, float flt_max, int dtype, float* d_scale,
                                           void* stream);
 
+/* Per-tensor `mean` scaling of quantize_tensor (mpemu/qutils.py:276-281), on the device, no host sync:
+ *     mean = mean|x|;  mean = flt_min if not |mean| > mean_floor;  *d_scale = max(1, flt_min / mean)
+ * (the division evaluated like torch's for a 0-dim tensor: reciprocal * flt_min in the tensor's element type).
+ * Two launches, deterministic (fixed partial-sum assignment, double accumulation).  d_work: device scratch of
+ * fpemu_mean_scale_work_bytes() bytes, 8-byte aligned. */
+FPEMU_API int fpemu_mean_scale_work_bytes(void);
+FPEMU_API int fpemu_scale_from_abs_mean(const void* in, int64_t n, int dtype, float flt_min, float mean_floor, void* d_work,
+                                        float* d_scale, void* stream);
+
+/* *d_scale = the blocked mode's power-of-two scale 2*2^floor(log2 amax)/K (fpemu_kernels.cu:409-413, 577-581, 909-911;
+ * FP4: 1/amax, :998) for ONE block whose maximum is *d_amax — used when a single block spans a whole large tensor
+ * (block_size == size, the reference CPU op's reading, cpp/fpemu_impl.cpp:778-779): fpemu_amax, this, fpemu_cast. */
+FPEMU_API int fpemu_block_scale_from_amax(const float* d_amax, int format, int dtype, float* d_scale, void* stream);
+
 /* Per-tensor amax-scaled cast in one call (the per-tensor `max` branch of quantize_tensor, mpemu/qutils.py:274-287):
  * clears d_work[0..1], reduces max|x| into d_work[0] and casts with the scale fpemu_scale_from_amax_dtype defines,
  * which the cast kernel derives itself and stores in d_work[1].  d_work: two device floats owned by the caller (scratch; calls that

@@ -321,6 +321,95 @@ def test_per_channel_mean_scaling_for_every_format_that_takes_a_scale(mp, dtype,
     assert torch.equal(got.view(torch.int32), want.view(torch.int32))
 
 
+def test_batched_hook_launches_equal_the_per_tensor_hooks(mp):
+    """The hook layer casts the weights of all hooked modules in one sweep when the root forward starts, and the weight
+    gradients in one sweep when the backward pass ends (qutils._WeightBatch / _GradBatch).  With every gradient config
+    switched to a deterministic rounding, a training step must be bit-identical with and without the batching; the
+    number of per-tensor casts drops by (number of weights - 1) per sweep."""
+    from mpemu import mpt_emu, qutils
+    import fpemu_b200 as F
+
+    def run(batched):
+        qutils.set_batched_hooks(batched)
+        try:
+            m = models.make("mlp").train().cuda()
+            m, emu = mpt_emu.initialize(m, None, training_algo="hybrid", list_exempt_layers=["head"], device="cuda")
+            for mod in m.modules():
+                qc = getattr(mod, "qconfig", None)
+                if qc is not None:
+                    for role in ("igrad_qconfig", "ograd_qconfig", "wtgrad_qconfig"):
+                        if getattr(qc, role) is not None:
+                            getattr(qc, role).scheme = "rne"
+            calls = {"single": 0, "sweeps": 0}
+            orig_q, orig_s = qutils.quantize_tensor, F.MultiTensorPlan.amax_scaled_cast
+            orig_c = F.MultiTensorPlan.cast
+
+            def spy_q(*a, **k):
+                calls["single"] += 1
+                return orig_q(*a, **k)
+
+            def spy_s(self, *a, **k):
+                calls["sweeps"] += 1
+                return orig_s(self, *a, **k)
+
+            def spy_c(self, *a, **k):
+                calls["sweeps"] += 1
+                return orig_c(self, *a, **k)
+            qutils.quantize_tensor, F.MultiTensorPlan.amax_scaled_cast, F.MultiTensorPlan.cast = spy_q, spy_s, spy_c
+            try:
+                ids = torch.randint(0, 100, (8, 12), generator=torch.Generator().manual_seed(3)).cuda()
+                tgt = torch.randint(0, 4, (8,), generator=torch.Generator().manual_seed(4)).cuda()
+                outs = []
+                for _ in range(2):                       # second step: gradients of step one are still in .grad
+                    logits = m(ids)
+                    torch.nn.functional.cross_entropy(logits, tgt).backward()
+                    outs.append(logits.detach().clone())
+            finally:
+                qutils.quantize_tensor, F.MultiTensorPlan.amax_scaled_cast, F.MultiTensorPlan.cast = orig_q, orig_s, orig_c
+            return outs, [p.detach().clone() for p in m.parameters()], [p.grad.clone() for p in m.parameters()], calls
+        finally:
+            qutils.set_batched_hooks(True)
+    o1, w1, g1, c1 = run(False)
+    o2, w2, g2, c2 = run(True)
+    for a, b in zip(o1 + w1 + g1, o2 + w2 + g2):
+        assert torch.equal(a.view(torch.int32), b.view(torch.int32))
+    assert c1["sweeps"] == 0
+    # mlp: 3 hooked modules with weights (fc1, norm has none cast, fc2; embeddings / head differ) -> at least one weight
+    # sweep per forward and one gradient sweep in the first backward (the second backward accumulates: immediate casts)
+    assert c2["sweeps"] >= 3 and c2["single"] < c1["single"]
+
+
+@pytest.mark.parametrize("dt", [torch.float32, torch.float16, torch.bfloat16])
+def test_mean_scale_kernel_equals_the_reference_expression(mp, dt):
+    """qutils.py:276-281 on the device in two small kernels: same scale as the torch expression the reference runs
+    (bit-exact whenever that expression's own reduction order does not decide, i.e. always when the scale clamps to 1),
+    and the cast with it equals the oracle."""
+    import fpemu_b200 as F
+    from mpemu.qutils import TensorQuantConfig, quantize_tensor
+    flt_min = 1.5258789e-05
+    for n, amp in ((100003, 1.0), (4096, 1.5e-5), (1 << 20, 1.4e-5), (777, 0.0), (50000, 1e-7), (300001, 1.7e-5)):
+        if dt == torch.float16 and 1e-6 < amp < 1e-3:
+            continue                                        # 1 / mean overflows half upstream (scale inf: exit(1) there)
+        x = (torch.randn(n, device="cuda") * amp).to(dt)
+        got = F.mean_scale(x, flt_min).item()
+        mean = torch.mean(abs(torch.flatten(x)))
+        mean = abs(mean) if abs(mean) > 1e-5 else flt_min
+        scale = flt_min / abs(mean) if abs(mean) > 0.0 else 1.0
+        scale = 1.0 if scale < 1.0 else scale
+        want = float(scale)
+        if dt == torch.bfloat16 and want != 1.0:
+            continue                                        # upstream does not dispatch bfloat16: float arithmetic here
+        assert abs(got - want) <= 2e-3 * want if dt == torch.float16 else abs(got - want) <= 1e-6 * want, (n, amp, got, want)
+        if amp == 1.0 or amp == 0.0 or amp == 1e-7:
+            assert got == 1.0
+    x = torch.randn(70001, device="cuda") * 1.5e-5
+    cfg = TensorQuantConfig("e5m2", "rne", "per-tensor-mean")
+    q = quantize_tensor(x, cfg, None)
+    s = F.mean_scale(x, flt_min)
+    assert s.item() > 1.0
+    assert torch.equal(q, F.cast(x, "E5M2_RNE", d_scale=s, unscale_fp32=True))
+
+
 def test_emulated_training_step_as_one_cuda_graph(mp):
     """Forward, backward (with the E5M2-stochastic gradient hooks) and optimizer step captured once and replayed:
     nothing in the hook layer or the library synchronises or allocates outside the graph's pool.  Two identically

@@ -107,7 +107,11 @@ def test_bert_base_hybrid_every_hooked_module(mp):
         seen.append(role)
         if len(seen) % 7 == 1:                       # every 7th gradient cast gets the full property check
             e5m2_stochastic_properties(role, src, out, qc)
-    digests, log = teacher.drive(model, qutils, names, shapes, "cuda", training=True, on_stochastic=on_stochastic)
+    qutils.set_batched_hooks(False)                  # per-tensor hook behaviour: every cast goes through quantize_tensor
+    try:
+        digests, log = teacher.drive(model, qutils, names, shapes, "cuda", training=True, on_stochastic=on_stochastic)
+    finally:
+        qutils.set_batched_hooks(True)
     compare(digests, want, log, want_log)
     assert len(seen) == sum("stochastic" in s for s in want_log) == 97 + 97 + 72    # ograd, igrad, wtgrad
 
