@@ -241,6 +241,24 @@ class _ScaledCast(torch.autograd.Function):
         return grad, None, None, None, None, None, None, None
 
 
+def _rows_mode_scaled(tensor, mode, inplace, rows, cols, flt_min):
+    """`mean` scaling over dim-0 channels or fine-grained groups: the reference takes the *mode* of each row
+    (qutils.py:297, :321) and calls the op once per row.  Same numbers from ONE torch.mode over dim 1 (checked equal to
+    the per-row calls, ties included), the scale expression of :298-301 on the device, and one row-wise launch with
+    those scales: no .item()."""
+    src = tensor.detach()
+    src = src if src.is_contiguous() else src.contiguous()
+    m = torch.abs(torch.mode(src.reshape(rows, cols), dim=1).values).float()
+    m = torch.where(m > 1e-6, m, torch.full_like(m, flt_min))
+    scales = torch.clamp(flt_min / m, min=1.0).contiguous()
+    out = src if (inplace and src.data_ptr() == tensor.data_ptr()) else torch.empty_like(src)
+    _F.cast_rows_scaled(src, mode, scales, out=out, rows=rows, cols=cols, unscale_fp32=_UNSCALE_FP32)
+    if inplace and out.data_ptr() != tensor.data_ptr():
+        tensor.copy_(out)
+        return tensor
+    return tensor if inplace else out
+
+
 def _supported_dtype(t):
     return t.dtype in (torch.float32, torch.float16, torch.bfloat16)
 
@@ -289,17 +307,7 @@ def quantize_tensor(tensor, qtconfig, qtparams, inplace=False):
             # scale expression of :298-301 on the device, and one row-wise launch with those scales: no .item().
             flt_min = qtconfig.get_flt_min()
             if takes_scale and _supported_dtype(tensor) and channels > 0 and cols > 0:     # incl. E4M3_IEEE, FP4
-                src = tensor.detach()
-                src = src if src.is_contiguous() else src.contiguous()
-                m = torch.abs(torch.mode(src.reshape(channels, cols), dim=1).values).float()
-                m = torch.where(m > 1e-6, m, torch.full_like(m, flt_min))
-                scales = torch.clamp(flt_min / m, min=1.0).contiguous()
-                out = src if (inplace and src.data_ptr() == tensor.data_ptr()) else torch.empty_like(src)
-                _F.cast_rows_scaled(src, mode, scales, out=out, rows=channels, cols=cols, unscale_fp32=_UNSCALE_FP32)
-                if inplace and out.data_ptr() != tensor.data_ptr():
-                    tensor.copy_(out)
-                    return tensor
-                return tensor if inplace else out
+                return _rows_mode_scaled(tensor, mode, inplace, channels, cols, flt_min)
             out = tensor if inplace else torch.zeros_like(tensor)
             for c in range(channels):
                 sub = tensor.select(0, c).detach()
@@ -321,6 +329,10 @@ def quantize_tensor(tensor, qtconfig, qtparams, inplace=False):
                 and tensor.dim() > 1 and in_ch % chunks == 0):
             rows = k * chunks
             return _scaled_cast(tensor, mode, inplace, "rows", flt_max, rows, tensor.numel() // rows, False)
+        if (qtconfig.scaling_method == "mean" and takes_scale and _supported_dtype(tensor)
+                and tensor.dim() > 1 and in_ch % chunks == 0 and tensor.numel() > 0):
+            rows = k * chunks                               # the same groups, `mean` (torch.mode) scaling: one launch
+            return _rows_mode_scaled(tensor, mode, inplace, rows, tensor.numel() // rows, qtconfig.get_flt_min())
         out = tensor if inplace else tensor.clone()
         for kk in range(k):
             crs = out.select(0, kk)

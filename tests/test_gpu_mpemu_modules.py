@@ -411,6 +411,28 @@ def test_mean_scale_kernel_equals_the_reference_expression(mp, dt):
     assert torch.equal(q, F.cast(x, "E5M2_RNE", d_scale=s, unscale_fp32=True))
 
 
+def test_fine_grained_groups_with_mean_scaling_equal_the_group_loop(mp):
+    """qutils.py:313-337 with scaling_method 'mean' (reachable by setting the attribute): torch.mode of every group,
+    scale = max(1, flt_min / |mode|), one op call per group upstream — one launch here, same bits."""
+    from mpemu import qutils
+    import fpemu_b200 as F
+    w = torch.randn(6, 32, 3, 3, device="cuda", generator=torch.Generator(device="cuda").manual_seed(8)) * 0.004
+    w[0, :8] = 0.001953125                                   # a group with a real mode
+    cfg = qutils.TensorQuantConfig("e4m3", "rne", "fine-grained", 8)
+    cfg.scaling_method = "mean"
+    got = qutils.quantize_tensor(w, cfg, None, inplace=False)
+    flt_min = cfg.get_flt_min()
+    want = w.clone()
+    for k in range(w.shape[0]):
+        for sub in want.select(0, k).chunk(max(1, int(w.shape[1] / 8)), 0):
+            mean = abs(torch.mode(torch.flatten(sub)).values)
+            mean = abs(mean) if abs(mean) > 1e-6 else flt_min
+            scale = flt_min / abs(mean)
+            scale = 1.0 if scale < 1.0 else scale
+            sub.copy_(F.cast(sub.contiguous(), "E4M3_RNE", scale=float(scale), unscale_fp32=True))
+    assert torch.equal(got.view(torch.int32), want.view(torch.int32))
+
+
 def test_emulated_training_step_as_one_cuda_graph(mp):
     """Forward, backward (with the E5M2-stochastic gradient hooks) and optimizer step captured once and replayed:
     nothing in the hook layer or the library synchronises or allocates outside the graph's pool.  Two identically
