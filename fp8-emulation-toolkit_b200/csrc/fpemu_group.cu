@@ -69,6 +69,8 @@ typedef void (*GroupKernel)(const CastArgs, const int64_t, const int, const int,
 
 template <int FMT, int RND, int DT>
 static GroupKernel pick_g(int r) {
+  if (r == 2) return group_reg_kernel<FMT, RND, DT, 2>;
+  if (r == 3) return group_reg_kernel<FMT, RND, DT, 3>;
   if (r == 4) return group_reg_kernel<FMT, RND, DT, 4>;
   if (r == 6) return group_reg_kernel<FMT, RND, DT, 6>;
   return group_reg_kernel<FMT, RND, DT, 8>;
@@ -96,7 +98,7 @@ static GroupKernel pick_rnd(int rnd, int dt, int r) {
 bool launch_group_reg(const CastArgs& a, int dtype, int64_t groups, int64_t vectors_per_group, int rule, float flt_max,
                       float* d_scale_out, cudaStream_t stream, int* status) {
   int lg, r;
-  if (!group_shape(vectors_per_group, &lg, &r)) return false;
+  if (!group_shape_tight(vectors_per_group, &lg, &r)) return false;
   GroupKernel k = nullptr;
   switch (a.fmt) {
     case FPEMU_FMT_E5M2: k = pick_rnd<FPEMU_FMT_E5M2>(a.rnd, dtype, r); break;

@@ -40,4 +40,24 @@ inline bool group_shape(int64_t vpg, int* lg, int* r) {
   return true;
 }
 
+// The same choice with 2 and 3 vectors per thread allowed as well (fpemu_group.cu has those instantiations): the shape
+// with the fewest idle vector slots, ties to the narrower group.  Rows whose length is not a power of two
+// (576, 4608, 11 008 ...) otherwise leave up to half of the slots of a 4-per-thread shape empty, and the registers those
+// slots hold are what limits the resident warps.
+inline bool group_shape_tight(int64_t vpg, int* lg, int* r) {
+  if (vpg < 1 || vpg > 256 * 8) return false;
+  static const int kR[] = {2, 3, 4, 6, 8};
+  int64_t best_slots = -1;
+  for (int l = 3; l <= 8; ++l) {
+    for (int ri = 0; ri < 5; ++ri) {
+      const int64_t slots = (int64_t)kR[ri] << l;
+      if (slots < vpg) continue;
+      if (kR[ri] > 4 && l < 8) continue;                         // 6 / 8 per thread only when 256 threads are not enough
+      if (best_slots < 0 || slots < best_slots) { best_slots = slots; *lg = l; *r = kR[ri]; }
+      break;                                                     // larger R at this width only adds idle slots
+    }
+  }
+  return best_slots >= 0;
+}
+
 }  // namespace fpemu

@@ -29,7 +29,7 @@ def timed(fn, nbuf, reps=30):
 rows_out = []
 for dname, dtype in (("fp32", torch.float32), ("bf16", torch.bfloat16)):
     esz = 4 if dtype == torch.float32 else 2
-    for cols in (576, 1024, 2048, 4096, 8192, 11008, 16384):
+    for cols in (576, 1024, 2048, 4096, 4608, 8192, 11008, 16384):
         rows = max(64, (1 << 27) // cols)                     # ~128 Mi elements per tensor
         n = rows * cols
         nbuf = max(2, min(8, (600 << 20) // (n * esz * 2)))
