@@ -57,9 +57,50 @@ __device__ __forceinline__ int mt_find(const void* table, int count, uint32_t b)
 // Scale of tensor t: the caller's d_scales[t], or — when the launch was given the vector of absolute maxima instead
 // (proto.d_amax) — derived here exactly as fpemu_scale_from_amax_dtype does, so that an amax-scaled sweep over a tensor
 // list needs no separate scale launch; the tensor's first CTA stores the scale it used into proto.d_scale_out[t].
+//
+// Exchange mode (row-sharded lists, fpemu_cast_multi_xchg): proto.in is non-null and points at this rank's arrival flags
+// for the sweep's parity (uint32[world]), proto.n holds the world size, proto.elem_offset the sweep's epoch, and
+// proto.d_amax is this rank's receive area float[world][count], into which every rank's amax_multi_push_kernel has
+// written (or is about to write) its local maxima over NVLink.  The CTA waits until all flags carry the epoch, then
+// takes the maximum over ranks of tensor t's entries — the all-reduce(MAX) of the sharded sweep, done by the kernels
+// that produce and consume the vector instead of a collective launched between them.
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
+}
+
 template <int DT>
-__device__ __forceinline__ float mt_scale(const CastArgs& proto, const float* d_scales, int t, bool first_cta) {
+__device__ __forceinline__ float mt_scale(const CastArgs& proto, const float* d_scales, int t, int count, bool first_cta) {
   if (proto.d_amax == nullptr) return __ldg(d_scales + t);
+  if (proto.in != nullptr) {
+    __shared__ uint32_t s_amax_bits;
+    const int world = (int)proto.n;
+    const uint32_t epoch = (uint32_t)proto.elem_offset;
+    if (threadIdx.x < 32) {
+      uint32_t bits = 0u;
+      if ((int)threadIdx.x < world) {
+        const uint32_t* flag = static_cast<const uint32_t*>(proto.in) + threadIdx.x;
+        const long long t0 = clock64();
+        bool ok = true;
+        while (ld_acquire_sys(flag) != epoch) {
+          if (clock64() - t0 > 20000000000LL) { ok = false; break; }   // ~10 s: a peer died; poison instead of hanging
+          __nanosleep(64);
+        }
+        const volatile uint32_t* recv = reinterpret_cast<const volatile uint32_t*>(proto.d_amax);
+        bits = ok ? recv[(size_t)threadIdx.x * (size_t)count + (size_t)t] : 0x7FFFFFFFu;
+      }
+      bits = warp_max_u32(bits);                               // NaN patterns sort above everything: they propagate
+      if (threadIdx.x == 0) s_amax_bits = bits;
+    }
+    __syncthreads();
+    const float s = scale_from_amax(__uint_as_float(s_amax_bits), proto.flt_max, true, DT);
+    if (proto.d_scale_out != nullptr && first_cta && threadIdx.x == 0) proto.d_scale_out[t] = s;
+    return s;
+  }
   const float s = scale_from_amax(__ldg(proto.d_amax + t), proto.flt_max, true, DT);
   if (proto.d_scale_out != nullptr && first_cta && threadIdx.x == 0) proto.d_scale_out[t] = s;
   return s;
@@ -82,7 +123,7 @@ __global__ void __launch_bounds__(kThreads) cast_multi_kernel(const void* table,
   sc.unscale32 = (a.flags & FPEMU_FLAG_UNSCALE_FP32) != 0;
   const int64_t local_cta = (int64_t)(blockIdx.x - e.cta_cast);
   if (SCALED) {
-    const float s = effective_scale(mt_scale<DT>(proto, d_scales, t, local_cta == 0), DT);
+    const float s = effective_scale(mt_scale<DT>(proto, d_scales, t, count, local_cta == 0), DT);
     sc.scale = s;
     sc.rscale = __frcp_rn(s);
   }
@@ -148,7 +189,7 @@ __global__ void __launch_bounds__(kThreads) encode_multi_kernel(const void* tabl
   sc.scale = 1.0f; sc.rscale = 1.0f; sc.unscale32 = false;
   const int64_t local_cta = (int64_t)(blockIdx.x - e.cta_cast);
   if (SCALED) {
-    const float s = effective_scale(mt_scale<DT>(proto, d_scales, t, local_cta == 0), DT);
+    const float s = effective_scale(mt_scale<DT>(proto, d_scales, t, count, local_cta == 0), DT);
     sc.scale = s;
     sc.rscale = __frcp_rn(s);
   }
@@ -157,7 +198,7 @@ __global__ void __launch_bounds__(kThreads) encode_multi_kernel(const void* tabl
 }
 
 template <int DT>
-__global__ void __launch_bounds__(kThreads) amax_multi_kernel(const void* table, const int count, float* d_amax) {
+__device__ __forceinline__ void amax_multi_body(const void* table, const int count, float* d_amax) {
   constexpr int VE = DtInfo<DT>::kVecElems;
   const int t = mt_find<true>(table, count, blockIdx.x);
   const MtEntry e = mt_entries(table)[t];
@@ -190,6 +231,56 @@ __global__ void __launch_bounds__(kThreads) amax_multi_kernel(const void* table,
     unsigned int* dst = reinterpret_cast<unsigned int*>(d_amax + t);
     if (threadIdx.x == 0 && bits > *reinterpret_cast<volatile unsigned int*>(dst)) atomicMax(dst, bits);
   }
+}
+
+template <int DT>
+__global__ void __launch_bounds__(kThreads) amax_multi_kernel(const void* table, const int count, float* d_amax) {
+  amax_multi_body<DT>(table, count, d_amax);
+}
+
+// The exchange step of a row-sharded sweep, fused into the reduction: the same per-tensor maxima as amax_multi_kernel,
+// and the LAST CTA of the launch to finish (a device counter decides) pushes the finished local vector into every
+// rank's receive area over NVLink (plain stores to peer-mapped memory), fences at system scope and raises this rank's
+// arrival flag there.  It also re-zeroes the local vector and the counter, so the next sweep needs no memset.
+struct MtPeers {
+  float* recv[16];          // rank r's receive area for this parity, float[world][count], as mapped into this process
+  uint32_t* flags[16];      // rank r's arrival flags for this parity, uint32[world]
+  int world, rank;
+  uint32_t epoch;
+};
+
+__device__ __forceinline__ void mt_push(const int count, float* d_amax, unsigned int* d_counter, const MtPeers& peers) {
+  __threadfence();
+  volatile uint32_t* local = reinterpret_cast<volatile uint32_t*>(d_amax);
+  for (int t = threadIdx.x; t < count; t += kThreads) {
+    const uint32_t bits = local[t];
+    local[t] = 0u;
+    for (int r = 0; r < peers.world; ++r)
+      reinterpret_cast<volatile uint32_t*>(peers.recv[r])[(size_t)peers.rank * count + t] = bits;
+  }
+  __threadfence_system();
+  __syncthreads();
+  if ((int)threadIdx.x < peers.world) st_release_sys(peers.flags[threadIdx.x] + peers.rank, peers.epoch);
+  if (threadIdx.x == 0) *d_counter = 0u;
+}
+
+template <int DT>
+__global__ void __launch_bounds__(kThreads) amax_multi_push_kernel(const void* table, const int count, float* d_amax,
+                                                                  unsigned int* d_counter, const MtPeers peers) {
+  amax_multi_body<DT>(table, count, d_amax);
+  __shared__ bool s_last;
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) s_last = (atomicAdd(d_counter, 1u) == gridDim.x - 1);
+  __syncthreads();
+  if (!s_last) return;
+  mt_push(count, d_amax, d_counter, peers);
+}
+
+// A rank whose slabs are all empty still has to arrive.
+__global__ void __launch_bounds__(kThreads) push_only_kernel(const int count, float* d_amax, unsigned int* d_counter,
+                                                            const MtPeers peers) {
+  mt_push(count, d_amax, d_counter, peers);
 }
 
 typedef void (*MultiCastKernel)(const void*, const int, const CastArgs, const float*);
@@ -297,7 +388,7 @@ namespace {
 // Shared body of the four list launches: values or codes, scales given or derived from a vector of maxima.
 int launch_multi(bool codes, const void* d_table, const void* h_table, int count, int format, int rounding, int flags,
                  const float* d_scales, const float* d_amax, float flt_max, float* d_scales_out, uint64_t seed,
-                 void* stream_) {
+                 void* stream_, const uint32_t* xchg_flags = nullptr, int world = 0, uint32_t epoch = 0) {
   if (d_table == nullptr || h_table == nullptr || count <= 0) return FPEMU_ERR_ARG;
   const MtHeader* h = static_cast<const MtHeader*>(h_table);
   if (h->count != count) return FPEMU_ERR_ARG;
@@ -330,10 +421,10 @@ int launch_multi(bool codes, const void* d_table, const void* h_table, int count
   if (k == nullptr) return FPEMU_ERR_MODE;                       // rare modes: use the per-tensor entry point
   if (h->total_cast == 0) return FPEMU_OK;
   CastArgs proto;
-  proto.in = nullptr; proto.out = nullptr; proto.n = 0;
+  proto.in = xchg_flags; proto.out = nullptr; proto.n = world;       // exchange mode: see mt_scale()
   proto.scale = 1.0f; proto.d_scale = nullptr;
   proto.seed_lo = (uint32_t)seed; proto.seed_hi = (uint32_t)(seed >> 32);
-  proto.elem_offset = 0;
+  proto.elem_offset = epoch;
   proto.fmt = format; proto.rnd = rounding; proto.flags = flags;
   proto.d_amax = d_amax; proto.flt_max = flt_max; proto.d_scale_out = d_scales_out; proto.d_seed = seed_source();
   k<<<h->total_cast, kThreads, 0, static_cast<cudaStream_t>(stream_)>>>(d_table, count, proto, d_scales);
@@ -366,4 +457,68 @@ extern "C" int fpemu_encode_multi_amax(const void* d_table, const void* h_table,
   if (d_amax == nullptr) return FPEMU_ERR_ARG;
   return launch_multi(true, d_table, h_table, count, format, rounding, flags, nullptr, d_amax, flt_max, d_scales_out, seed,
                       stream_);
+}
+
+// ---- exchange of the maxima over peer memory (row-sharded lists on the GPUs of one NVLink domain) ----------------------
+// Exchange buffer of one rank, in floats: recv[parity 0..1][source rank][count], then flags[parity][source rank].
+extern "C" int64_t fpemu_exchange_floats(int count, int world) {
+  if (count <= 0 || world <= 0 || world > 16) return FPEMU_ERR_ARG;
+  return 2LL * world * count + 2LL * world;
+}
+
+extern "C" int fpemu_amax_multi_push(const void* d_table, const void* h_table, int count, float* d_amax,
+                                     unsigned int* d_counter, void* const* peer_bufs, int world, int rank, uint32_t epoch,
+                                     void* stream_) {
+  if (d_table == nullptr || h_table == nullptr || d_amax == nullptr || d_counter == nullptr || peer_bufs == nullptr ||
+      count <= 0 || world <= 0 || world > 16 || rank < 0 || rank >= world || epoch == 0)
+    return FPEMU_ERR_ARG;
+  const MtHeader* h = static_cast<const MtHeader*>(h_table);
+  if (h->count != count) return FPEMU_ERR_ARG;
+  MtPeers peers;
+  const int parity = (int)(epoch & 1u);
+  for (int r = 0; r < 16; ++r) { peers.recv[r] = nullptr; peers.flags[r] = nullptr; }
+  for (int r = 0; r < world; ++r) {
+    if (peer_bufs[r] == nullptr) return FPEMU_ERR_ARG;
+    float* base = static_cast<float*>(peer_bufs[r]);
+    peers.recv[r] = base + (size_t)parity * world * count;
+    peers.flags[r] = reinterpret_cast<uint32_t*>(base + 2 * (size_t)world * count) + (size_t)parity * world;
+  }
+  peers.world = world; peers.rank = rank; peers.epoch = epoch;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (h->total_amax == 0) {
+    push_only_kernel<<<1, kThreads, 0, stream>>>(count, d_amax, d_counter, peers);
+    return (int)cudaGetLastError();
+  }
+  switch (h->dtype & 0xFF) {
+    case FPEMU_DT_F32:  amax_multi_push_kernel<FPEMU_DT_F32><<<h->total_amax, kThreads, 0, stream>>>(d_table, count, d_amax, d_counter, peers); break;
+    case FPEMU_DT_F16:  amax_multi_push_kernel<FPEMU_DT_F16><<<h->total_amax, kThreads, 0, stream>>>(d_table, count, d_amax, d_counter, peers); break;
+    default:            amax_multi_push_kernel<FPEMU_DT_BF16><<<h->total_amax, kThreads, 0, stream>>>(d_table, count, d_amax, d_counter, peers); break;
+  }
+  return (int)cudaGetLastError();
+}
+
+static int launch_xchg(bool codes, const void* d_table, const void* h_table, int count, int format, int rounding, int flags,
+                       const void* my_buf, int world, uint32_t epoch, float flt_max, float* d_scales_out, uint64_t seed,
+                       void* stream_) {
+  if (my_buf == nullptr || world <= 0 || world > 16 || epoch == 0 || count <= 0) return FPEMU_ERR_ARG;
+  const int parity = (int)(epoch & 1u);
+  const float* base = static_cast<const float*>(my_buf);
+  const float* recv = base + (size_t)parity * world * count;
+  const uint32_t* flg = reinterpret_cast<const uint32_t*>(base + 2 * (size_t)world * count) + (size_t)parity * world;
+  return launch_multi(codes, d_table, h_table, count, format, rounding, flags, nullptr, recv, flt_max, d_scales_out, seed,
+                      stream_, flg, world, epoch);
+}
+
+extern "C" int fpemu_cast_multi_xchg(const void* d_table, const void* h_table, int count, int format, int rounding,
+                                     int flags, const void* my_buf, int world, uint32_t epoch, float flt_max,
+                                     float* d_scales_out, uint64_t seed, void* stream_) {
+  return launch_xchg(false, d_table, h_table, count, format, rounding, flags, my_buf, world, epoch, flt_max, d_scales_out,
+                     seed, stream_);
+}
+
+extern "C" int fpemu_encode_multi_xchg(const void* d_table, const void* h_table, int count, int format, int rounding,
+                                       int flags, const void* my_buf, int world, uint32_t epoch, float flt_max,
+                                       float* d_scales_out, uint64_t seed, void* stream_) {
+  return launch_xchg(true, d_table, h_table, count, format, rounding, flags, my_buf, world, epoch, flt_max, d_scales_out,
+                     seed, stream_);
 }

@@ -28,6 +28,13 @@ class CudaKernels(object):
     encode = staticmethod(_ops.encode)
 
 
+def _as_bits(vec):
+    """The vector of maxima as int32 bit patterns: for non-negative floats the integer order is the numeric order and every
+    NaN pattern sorts above +Inf, so an integer MAX all-reduce propagates a NaN from any rank (what the kernels' own
+    reductions do), which a floating-point MAX does not promise."""
+    return vec.view(torch.int32)
+
+
 def _world(group):
     if dist.is_available() and dist.is_initialized():
         return dist.get_world_size(group), dist.get_rank(group)
@@ -45,7 +52,7 @@ def global_amax(slabs, group=None, kernels=CudaKernels, out=None):
             kernels.amax(x, out=vec[t:t + 1])
     world, _ = _world(group)
     if world > 1:
-        dist.all_reduce(vec, op=dist.ReduceOp.MAX, group=group)
+        dist.all_reduce(_as_bits(vec), op=dist.ReduceOp.MAX, group=group)
     return vec
 
 
@@ -68,7 +75,7 @@ def _sharded_amax_scaled(slabs, mode, row_offsets, cols, outs, group, seed, flt_
 
     def reduce_run(t0, t1):
         if world > 1:
-            return dist.all_reduce(vec[t0:t1], op=dist.ReduceOp.MAX, group=group, async_op=True)
+            return dist.all_reduce(_as_bits(vec[t0:t1]), op=dist.ReduceOp.MAX, group=group, async_op=True)
         return None
 
     def apply_run(t0, t1):
@@ -108,6 +115,61 @@ def sharded_amax_scaled_encode(slabs, mode, row_offsets=None, cols=None, outs=No
                                                            expect_normals=True))
 
 
+class PeerExchange(object):
+    """The all-reduce(MAX) of a sharded sweep done by the kernels on either side of it (fpemu_amax_multi_push /
+    fpemu_cast_multi_xchg): every rank owns an exchange buffer in symmetric memory (torch.distributed._symmetric_memory:
+    peer-mapped over NVLink), the amax launch's last CTA stores the local maxima into every rank's buffer and raises a
+    flag there, and the cast launch's CTAs wait for the flags and take the maximum over ranks themselves.  One sweep =
+    two launches, no collective, no memset.  Raises RuntimeError when symmetric memory is not available."""
+
+    def __init__(self, plan, group=None):
+        import ctypes
+        try:
+            import torch.distributed._symmetric_memory as symm_mem
+        except Exception as e:  # noqa: BLE001
+            raise RuntimeError("fpemu: torch symmetric memory is not available (%s)" % e)
+        self.plan = plan
+        self.world, self.rank = _world(group)
+        if self.world < 2 or self.world > 16:
+            raise RuntimeError("fpemu: the peer exchange needs 2..16 ranks")
+        grp = group if group is not None else dist.group.WORLD
+        nfl = int(L.lib().fpemu_exchange_floats(plan.count, self.world))
+        self.buf = symm_mem.empty(nfl, dtype=torch.float32, device=plan.device)
+        self.hdl = symm_mem.rendezvous(self.buf, grp.group_name)
+        self.buf.zero_()
+        torch.cuda.synchronize(plan.device)
+        self.hdl.barrier()                                   # every rank's flags are zero before anybody pushes
+        self.ptrs = (ctypes.c_void_p * self.world)(*[int(p) for p in self.hdl.buffer_ptrs])
+        self.local = torch.zeros(plan.count, dtype=torch.float32, device=plan.device)
+        self.counter = torch.zeros(1, dtype=torch.int32, device=plan.device)
+        self.epoch = 0
+
+    def sweep(self, mode, flt_max, seed, flags_extra=0):
+        """amax -> exchange -> cast / encode of the plan's tensors; returns (outs, scales).  Every rank must call the
+        sweeps of one PeerExchange in the same order."""
+        import ctypes
+        plan = self.plan
+        fmt, rnd, flags = L.parse_mode(mode)
+        if flt_max is None:
+            flt_max = _ops.FLT_MAX[fmt]
+        if rnd == L.RND_STOCHASTIC and seed is None:
+            seed = _ops.next_seed()
+        self.epoch += 1
+        scales = torch.empty(plan.count, dtype=torch.float32, device=plan.device)
+        stream = _ops._stream(plan.d_table)
+        with _ops._on_device(plan.d_table):
+            st = L.lib().fpemu_amax_multi_push(plan.d_table.data_ptr(), plan.h_table.data_ptr(), plan.count,
+                                               self.local.data_ptr(), self.counter.data_ptr(),
+                                               ctypes.addressof(self.ptrs), self.world, self.rank, self.epoch, stream)
+            L.check(st, "fpemu_amax_multi_push")
+            fn = L.lib().fpemu_encode_multi_xchg if plan.packed else L.lib().fpemu_cast_multi_xchg
+            st = fn(plan.d_table.data_ptr(), plan.h_table.data_ptr(), plan.count, fmt, rnd, flags | flags_extra,
+                    self.buf.data_ptr(), self.world, self.epoch, float(flt_max), scales.data_ptr(),
+                    int(seed or 0) & 0xFFFFFFFFFFFFFFFF, stream)
+            L.check(st, "fpemu_%s_multi_xchg(%s)" % ("encode" if plan.packed else "cast", mode))
+        return plan.outs, scales
+
+
 class ShardedPlan(object):
     """The multi-tensor version of sharded_amax_scaled_cast: the slab list is described to the library once and
     every sweep is then two launches per run of tensors (amax, cast — the cast kernel derives the scales) plus ONE
@@ -116,18 +178,30 @@ class ShardedPlan(object):
     launch, so it executes behind the next run's amax / the previous run's cast instead of idling the GPU between
     two kernels (tools/llama7b_sweep.py measures k = 1, 2, 4)."""
 
-    def __init__(self, slabs, row_offsets=None, cols=None, outs=None, group=None, pipeline=1):
+    def __init__(self, slabs, row_offsets=None, cols=None, outs=None, group=None, pipeline=1, exchange="nccl"):
+        """exchange: "nccl" (one all-reduce(MAX) between the two launches), "peer" (the exchange fused into the two
+        launches over peer memory, PeerExchange) or "auto" (peer when symmetric memory works here, else nccl)."""
         n = len(slabs)
         row_offsets = row_offsets or [0] * n
         cols = cols or [(x.shape[-1] if x.dim() > 1 else 1) for x in slabs]
         self.group = group
         self.pipeline = pipeline
         self.plan = _ops.MultiTensorPlan(slabs, outs, [r * c for r, c in zip(row_offsets, cols)])
+        self.peer = None
+        world, _ = _world(group)
+        if exchange not in ("nccl", "peer", "auto"):
+            raise ValueError("exchange must be 'nccl', 'peer' or 'auto'")
+        if exchange != "nccl" and world > 1:
+            try:
+                self.peer = PeerExchange(self.plan, group)
+            except Exception:  # noqa: BLE001
+                if exchange == "peer":
+                    raise
 
     def _allreduce(self, vec):
         world, _ = _world(self.group)
         if world > 1:
-            return dist.all_reduce(vec, op=dist.ReduceOp.MAX, group=self.group, async_op=True)
+            return dist.all_reduce(_as_bits(vec), op=dist.ReduceOp.MAX, group=self.group, async_op=True)
         return None
 
     def _depth(self):
@@ -135,6 +209,8 @@ class ShardedPlan(object):
         return self.pipeline if world > 1 else 1
 
     def amax_scaled_cast(self, mode, seed=0, flt_max=None, unscale_fp32=False):
+        if self.peer is not None:
+            return self.peer.sweep(mode, flt_max, seed, L.FLAG_UNSCALE_FP32 if unscale_fp32 else 0)
         return self.plan.amax_scaled_cast(mode, flt_max=flt_max, seed=seed, reduce_fn=self._allreduce,
                                           unscale_fp32=unscale_fp32, pipeline=self._depth())
 
@@ -144,6 +220,8 @@ class ShardedPlan(object):
     def amax_scaled_encode(self, mode, seed=0, flt_max=None):
         """As amax_scaled_cast, for a plan whose outputs are uint8 code buffers: every rank ends up with the 8-bit
         codes of its slabs and the same float32[T] scale vector."""
+        if self.peer is not None:
+            return self.peer.sweep(mode, flt_max, seed, L.FLAG_EXPECT_NORMALS)
         return self.plan.amax_scaled_encode(mode, flt_max=flt_max, seed=seed, reduce_fn=self._allreduce,
                                             pipeline=self._depth())
 

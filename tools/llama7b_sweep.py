@@ -28,7 +28,8 @@ def main():
     ap.add_argument("--mode", default="E4M3_RNE")
     ap.add_argument("--multi", action="store_true", help="multi-tensor launches instead of 2 x 291 + 1 per-tensor launches")
     ap.add_argument("--packed", action="store_true", help="write 8-bit codes instead of de-quantised values (implies --multi)")
-    ap.add_argument("--pipeline", default="2", help="runs of tensors per sweep, comma-separated list to sweep (e.g. 1,2,4)")
+    ap.add_argument("--exchange", default="auto", choices=["auto", "nccl", "peer"])
+    ap.add_argument("--pipeline", default="1", help="runs of tensors per sweep, comma-separated list to sweep (e.g. 1,2,4)")
     args = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -40,7 +41,7 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
     for depth in [int(v) for v in args.pipeline.split(",")]:
         res = bench.c5_sweep(dev, world, rank, args.dtype, args.reps, depth, mode=args.mode, packed=args.packed,
-                             multi=args.multi or args.packed)
+                             multi=args.multi or args.packed, exchange=args.exchange)
         if rank == 0:
             print(json.dumps(res), flush=True)
     if world > 1:
