@@ -122,11 +122,6 @@ __global__ void __launch_bounds__(kThreads) cast_multi_kernel(const void* table,
   sc.scale = 1.0f; sc.rscale = 1.0f;
   sc.unscale32 = (a.flags & FPEMU_FLAG_UNSCALE_FP32) != 0;
   const int64_t local_cta = (int64_t)(blockIdx.x - e.cta_cast);
-  if (SCALED) {
-    const float s = effective_scale(mt_scale<DT>(proto, d_scales, t, count, local_cta == 0), DT);
-    sc.scale = s;
-    sc.rscale = __frcp_rn(s);
-  }
   const int64_t nvec = a.n / VE;
   const char* in = static_cast<const char*>(a.in);
   char* out = static_cast<char*>(a.out);
@@ -136,6 +131,13 @@ __global__ void __launch_bounds__(kThreads) cast_multi_kernel(const void* table,
   for (int j = 0; j < U; ++j) {
     const int64_t vi = base + j * kThreads;
     if (vi < nvec) v[j] = ldg256(in + vi * 32);
+  }
+  // the scale AFTER the loads have been issued: in exchange mode it involves system-scope flag reads and a CTA barrier,
+  // whose latency would otherwise sit in front of every short-lived CTA's memory traffic
+  if (SCALED) {
+    const float s = effective_scale(mt_scale<DT>(proto, d_scales, t, count, local_cta == 0), DT);
+    sc.scale = s;
+    sc.rscale = __frcp_rn(s);
   }
 #pragma unroll
   for (int j = 0; j < U; ++j) {
