@@ -256,7 +256,7 @@ def llama7b_shapes():
 def c5_sweep(dev, world, rank, dtype_name, reps, pipeline, mode="E4M3_RNE", packed=False, multi=True, exchange="auto"):
     """One measurement of the C5 workload on this rank's row slabs; returns the result dict (same on every rank).
     exchange: how the float[291] vector of maxima is exchanged at N > 1 — "nccl" (one all-reduce between the two
-    launches), "peer" (fused into the two launches over NVLink peer memory), "auto" = both are timed, checked to give
+    launches), "peer" (pushed over NVLink peer memory behind the amax launch, awaited inside the cast launch), "auto" = both are timed, checked to give
     identical scales and outputs, and the faster one is reported as `ms_per_sweep`."""
     import torch
     import torch.distributed as dist
@@ -306,21 +306,27 @@ def c5_sweep(dev, world, rank, dtype_name, reps, pipeline, mode="E4M3_RNE", pack
     timings, plan = {}, None
     if multi or packed:
         kinds = ["nccl"] if (world == 1 or exchange == "nccl") else (["peer"] if exchange == "peer" else ["nccl", "peer"])
-        ref = None
+        plans, ref = {}, None
         for kind in kinds:
             try:
-                plan = fd.ShardedPlan(slabs, row_offsets=offsets, cols=cols, outs=outs, pipeline=pipeline, exchange=kind)
+                plans[kind] = fd.ShardedPlan(slabs, row_offsets=offsets, cols=cols, outs=outs, pipeline=pipeline, exchange=kind)
             except Exception as e:  # noqa: BLE001  (symmetric memory unavailable on this box)
                 timings[kind] = "unavailable: %s" % str(e)[:120]
-                continue
-            ms_k, scales_k, digest_k = measure(plan)
-            timings[kind] = ms_k
-            if ref is None:
-                ref = (scales_k, digest_k)
-            else:
-                assert torch.equal(ref[0].view(torch.int32), scales_k.view(torch.int32)) and ref[1] == digest_k, \
-                    "peer-memory exchange and NCCL all-reduce disagree"
-            del plan
+        # the exchanges alternate, round after round, and each reports its best round: whichever ran first would
+        # otherwise be measured on the cooler GPU (a B200 streaming at 7 TB/s loses ~5 % in its first second)
+        for rnd in range(3 if len(plans) > 1 else 1):
+            for kind in kinds:
+                if kind not in plans:
+                    continue
+                ms_k, scales_k, digest_k = measure(plans[kind])
+                timings[kind] = min(ms_k, timings.get(kind, ms_k))
+                if ref is None:
+                    ref = (scales_k, digest_k)
+                else:
+                    assert torch.equal(ref[0].view(torch.int32), scales_k.view(torch.int32)) and ref[1] == digest_k, \
+                        "peer-memory exchange and NCCL all-reduce disagree"
+        plan = plans.get(kinds[0])
+        plans = None
         best = min((k for k in timings if isinstance(timings[k], float)), key=lambda k: timings[k])
         ms = timings[best]
     else:
@@ -347,7 +353,7 @@ def c5_sweep(dev, world, rank, dtype_name, reps, pipeline, mode="E4M3_RNE", pack
            "allreduce_us": ar_us, "pipeline_runs": runs,
            "exchange": best if world > 1 else "none (one rank)",
            "ms_per_sweep_by_exchange": timings if world > 1 else None,
-           "launches_per_rank_per_sweep": (2 if (world > 1 and best == "peer") else 2 * runs + 1) if (multi or packed)
+           "launches_per_rank_per_sweep": (3 if (world > 1 and best == "peer") else 2 * runs + 1) if (multi or packed)
            else 3 * len(shapes) + 1,
            "scaling": "strong"}
     del slabs, outs

@@ -50,7 +50,7 @@ SIGNATURES = {
     "fpemu_cast_multi_amax": (_i32, [_vp, _vp, _i32, _i32, _i32, _i32, _vp, _f32, _vp, _u64, _vp]),
     "fpemu_encode_multi_amax": (_i32, [_vp, _vp, _i32, _i32, _i32, _i32, _vp, _f32, _vp, _u64, _vp]),
     "fpemu_exchange_floats": (_i64, [_i32, _i32]),
-    "fpemu_amax_multi_push": (_i32, [_vp, _vp, _i32, _vp, _vp, _vp, _i32, _i32, ctypes.c_uint32, _vp]),
+    "fpemu_amax_multi_push": (_i32, [_vp, _vp, _i32, _vp, _vp, _i32, _i32, ctypes.c_uint32, _vp]),
     "fpemu_cast_multi_xchg": (_i32, [_vp, _vp, _i32, _i32, _i32, _i32, _vp, _i32, ctypes.c_uint32, _f32, _vp, _u64, _vp]),
     "fpemu_encode_multi_xchg": (_i32, [_vp, _vp, _i32, _i32, _i32, _i32, _vp, _i32, ctypes.c_uint32, _f32, _vp, _u64, _vp]),
     "fpemu_encode": (_i32, [_vp, _vp, _i64, _i32, _i32, _i32, _i32, _f32, _vp, _u64, _u64, _vp]),

@@ -118,9 +118,10 @@ def sharded_amax_scaled_encode(slabs, mode, row_offsets=None, cols=None, outs=No
 class PeerExchange(object):
     """The all-reduce(MAX) of a sharded sweep done by the kernels on either side of it (fpemu_amax_multi_push /
     fpemu_cast_multi_xchg): every rank owns an exchange buffer in symmetric memory (torch.distributed._symmetric_memory:
-    peer-mapped over NVLink), the amax launch's last CTA stores the local maxima into every rank's buffer and raises a
-    flag there, and the cast launch's CTAs wait for the flags and take the maximum over ranks themselves.  One sweep =
-    two launches, no collective, no memset.  Raises RuntimeError when symmetric memory is not available."""
+    peer-mapped over NVLink), a one-CTA launch behind the amax launch stores the local maxima, each paired with the
+    sweep number in one 8-byte word, into every rank's buffer, and the cast launch's warps poll those words and take
+    the maximum over ranks themselves.
+    One sweep = amax, push, cast: no collective, no host synchronisation, no memset.  Raises RuntimeError when symmetric memory is not available."""
 
     def __init__(self, plan, group=None):
         import ctypes
@@ -138,10 +139,9 @@ class PeerExchange(object):
         self.hdl = symm_mem.rendezvous(self.buf, grp.group_name)
         self.buf.zero_()
         torch.cuda.synchronize(plan.device)
-        self.hdl.barrier()                                   # every rank's flags are zero before anybody pushes
+        self.hdl.barrier()                                   # every rank's buffer is zero before anybody pushes
         self.ptrs = (ctypes.c_void_p * self.world)(*[int(p) for p in self.hdl.buffer_ptrs])
-        self.local = torch.zeros(plan.count, dtype=torch.float32, device=plan.device)
-        self.counter = torch.zeros(1, dtype=torch.int32, device=plan.device)
+        self.local = torch.zeros(2 * plan.count, dtype=torch.float32, device=plan.device)
         self.epoch = 0
 
     def sweep(self, mode, flt_max, seed, flags_extra=0):
@@ -159,7 +159,7 @@ class PeerExchange(object):
         stream = _ops._stream(plan.d_table)
         with _ops._on_device(plan.d_table):
             st = L.lib().fpemu_amax_multi_push(plan.d_table.data_ptr(), plan.h_table.data_ptr(), plan.count,
-                                               self.local.data_ptr(), self.counter.data_ptr(),
+                                               self.local.data_ptr(),
                                                ctypes.addressof(self.ptrs), self.world, self.rank, self.epoch, stream)
             L.check(st, "fpemu_amax_multi_push")
             fn = L.lib().fpemu_encode_multi_xchg if plan.packed else L.lib().fpemu_cast_multi_xchg

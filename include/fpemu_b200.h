@@ -332,23 +332,27 @@ FPEMU_API int fpemu_encode_multi_amax(const void* d_table, const void* h_table, 
  * when the tensors of a list are row-sharded over the GPUs of one NVLink domain, the only communication
  * is an all-reduce(MAX) of the float[count] vector of maxima between the amax launch and the cast launch.  These entry
  * points remove the collective launch: every rank owns an exchange buffer of fpemu_exchange_floats(count, world)
- * floats that all ranks can address (peer-mapped / symmetric memory; zero it once, before the first sweep, and make
- * sure every rank has done so).  fpemu_amax_multi_push reduces like fpemu_amax_multi into d_amax (count floats, zero
- * before the first call — the call re-zeroes them) and the last CTA to finish stores the vector into EVERY rank's
- * buffer over NVLink and raises this rank's arrival flag there; d_counter: one zeroed device word.
- * fpemu_cast_multi_xchg / fpemu_encode_multi_xchg are fpemu_cast_multi_amax / fpemu_encode_multi_amax whose CTAs first
- * wait for all `world` flags of the sweep and then take the maximum over ranks themselves.
+ * floats (8-byte aligned) that all ranks can address (peer-mapped / symmetric memory; zero it once, before the first
+ * sweep, and make sure every rank has done so).  fpemu_amax_multi_push reduces like fpemu_amax_multi into one half of
+ * d_amax2 (2 x count floats, zero before the first call; the halves alternate with the epoch and the call re-zeroes
+ * the one the next sweep uses), and a small launch behind the reduction stores every maximum, paired with the sweep's
+ * epoch in one 8-byte word, into EVERY rank's buffer over NVLink.  The epoch travels with the value, so there is no
+ * separate arrival flag and no fence; the buffer holds several copies of the words so that the readers' polls spread
+ * over the L2 slices.
+ * fpemu_cast_multi_xchg / fpemu_encode_multi_xchg are fpemu_cast_multi_amax / fpemu_encode_multi_amax whose warps poll
+ * their tensor's `world` words until they carry the sweep's epoch and take the maximum over ranks themselves.
  *   peer_bufs  host array of `world` pointers: rank r's exchange buffer as mapped into THIS process
  *   my_buf     this rank's own exchange buffer
  *   epoch      sweep number, the same on every rank, starting at 1 and incremented per sweep (its parity selects one
  *              of two halves of the buffer, so a rank may run one sweep ahead of its peers)
- * A rank that never arrives would stall its peers: after about 10 s the waiting kernel gives up and poisons its scales
- * with NaN instead of hanging the GPU.  No counterpart in the reference (its only multi-GPU code is stock DDP in an
- * example script); the results equal the all-reduce path bit for bit. */
+ * A rank that never arrives would stall its peers: after about 10 s the waiting kernel gives up and poisons that rank's
+ * maxima with NaN for the epoch, so the launch ends (with NaN scales) instead of hanging the GPU.  No counterpart in
+ * the reference (its only multi-GPU code is stock DDP in an example script); the results equal the all-reduce path bit
+ * for bit.  With d_scales_out, the scales of tensors that have no elements on this rank are stored as well (all three
+ * of fpemu_*_multi_amax / _xchg). */
 FPEMU_API int64_t fpemu_exchange_floats(int count, int world);
-FPEMU_API int fpemu_amax_multi_push(const void* d_table, const void* h_table, int count, float* d_amax,
-                                    unsigned int* d_counter, void* const* peer_bufs, int world, int rank, uint32_t epoch,
-                                    void* stream);
+FPEMU_API int fpemu_amax_multi_push(const void* d_table, const void* h_table, int count, float* d_amax2,
+                                    void* const* peer_bufs, int world, int rank, uint32_t epoch, void* stream);
 FPEMU_API int fpemu_cast_multi_xchg(const void* d_table, const void* h_table, int count, int format, int rounding,
                                     int flags, const void* my_buf, int world, uint32_t epoch, float flt_max,
                                     float* d_scales_out, uint64_t seed, void* stream);

@@ -475,6 +475,17 @@ def test_multi_tensor_amax_scaled_cast_and_rejects_unaligned(F):
         want, ws = F.cast_amax_scaled(x, "E5M2_RNE", return_scale=True)
         assert ws.item() == s.item()
         assert_same(host(y), host(want), "amax-scaled multi, half")
+    # a tensor with no elements here (an empty row slab of a sharded list) has no CTA in the cast launch, but its
+    # scale — from the maximum the other ranks contributed — is still part of the result
+    xe = [xs[0], torch.empty(0, device="cuda"), xs[1]]
+    pe = F.MultiTensorPlan(xe, [torch.empty_like(x) for x in xe])
+
+    def other_ranks(v):
+        v[1:2].fill_(0.75)
+    for _ in range(2):
+        _, se = pe.amax_scaled_cast("E4M3_RNE", reduce_fn=other_ranks)
+        assert se[1].item() == F.scale_from_amax(torch.tensor([0.75], device="cuda"), 448.0).item()
+        assert se[0].item() == scales[0].item() and se[2].item() == scales[1].item()
     with pytest.raises(ValueError):
         F.MultiTensorPlan([xs[0][1:]])                                # not 32-byte aligned
     # element offsets that are not on a Philox-block boundary (slabs of a sharded tensor with an odd row length):

@@ -1,4 +1,4 @@
-"""The exchange step of a row-sharded sweep fused into its two kernels over peer memory (fpemu_amax_multi_push /
+"""The exchange step of a row-sharded sweep done by the kernels around it over peer memory (fpemu_amax_multi_push /
 fpemu_cast_multi_xchg, fpemu_b200.dist.PeerExchange) against the NCCL all-reduce path: two ranks on two GPUs (skipped on
 a one-GPU box; bench.py repeats the check at N > 1 where the driver's scaling run sees it).  Values, 8-bit codes and the
 scale vector must be identical bit for bit, sweep after sweep (the buffer halves alternate with the sweep number), with
@@ -74,15 +74,33 @@ def _worker(rank, world, port, q):
 def test_peer_exchange_equals_the_all_reduce_path_on_two_gpus():
     if torch.cuda.device_count() < 2:
         pytest.skip("needs two GPUs")
+    import queue
+    import time
     world = 2
     port = 29600 + (os.getpid() % 300)
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    procs = [ctx.Process(target=_worker, args=(r, world, port, q)) for r in range(world)]
+    procs = [ctx.Process(target=_worker, args=(r, world, port, q), daemon=True) for r in range(world)]
     for p in procs:
         p.start()
-    results = [q.get(timeout=300) for _ in range(world)]
-    for p in procs:
-        p.join(timeout=60)
+    results, deadline = [], time.time() + 200
+    try:
+        # a rank that fails leaves its peer waiting in a collective: report the first failure at once and stop the
+        # other rank, instead of waiting for a timeout the peer can never meet
+        while len(results) < world and time.time() < deadline:
+            try:
+                results.append(q.get(timeout=2))
+            except queue.Empty:
+                if any(p.exitcode not in (None, 0) for p in procs):
+                    break
+                continue
+            if results[-1][1] != "ok":
+                break
+    finally:
+        for p in procs:
+            p.join(timeout=20 if len(results) == world and all(m == "ok" for _, m in results) else 0.1)
+            if p.is_alive():
+                p.kill()                                   # this exact child, by handle
     for rank, msg in results:
         assert msg == "ok", "rank %d: %s" % (rank, msg)
+    assert len(results) == world, "ranks finished: %r, exit codes %r" % (results, [p.exitcode for p in procs])
