@@ -310,7 +310,8 @@ static CastKernel pick_kernel(int fmt, int rnd, bool daz, int dt, bool scaled, b
     case FPEMU_FMT_BF16: return pick_rnd<FPEMU_FMT_BF16>(rnd, false, dt, false, anyoff);
     case FPEMU_FMT_FP16: return pick_rnd<FPEMU_FMT_FP16>(rnd, false, dt, false, anyoff);
     case FPEMU_FMT_E4M3_IEEE: return daz ? nullptr : pick_rnd<FPEMU_FMT_E4M3_IEEE>(rnd, false, dt, scaled, anyoff);
-    default:             return nullptr;   // FP4 and anything without a packed kernel: generic kernel
+    case FPEMU_FMT_FP4:  return (rnd == FPEMU_RND_RNE && !daz) ? pick_dt<FPEMU_FMT_FP4, FPEMU_RND_RNE, false>(dt, scaled, false) : nullptr;
+    default:             return nullptr;   // anything without a packed kernel: generic kernel
   }
 }
 

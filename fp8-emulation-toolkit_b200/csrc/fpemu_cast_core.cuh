@@ -227,6 +227,24 @@ __device__ __forceinline__ void process_vec(Vec32& v, const ScaleCtx& sc, const 
       const uint32_t r2 = kSR ? __byte_perm(rw[k >> 1], 0u, (k & 1) ? 0x4342u : 0x4140u) : 0u;
       finish_pair<DT, SCALED>(v, k, round_pair<FMT, RND, DAZ>(h, r2), sc);
     }
+  } else if (FMT == FPEMU_FMT_FP4) {
+    // FP4_NEAREST (fpemu_kernels.cu:986-1024): `scale * in` in fp32, rounded on the upper halves of two products at a
+    // time (round_pair_fp4), un-scaled in fp32.  An unscaled bf16 tensor never leaves its own encoding.
+#pragma unroll
+    for (int k = 0; k < kPairs; ++k) {
+      if (DT == FPEMU_DT_BF16 && !SCALED) {
+        v.w[k] = round_pair_fp4(v.w[k]);
+      } else {
+        float2 f = get_pair<DT>(v, k);
+        // always a multiplication, as in the reference (by 1 when unscaled): it is what turns a NaN into +NaN
+        f.x = __fmul_rn(f.x, SCALED ? sc.scale : 1.0f);
+        f.y = __fmul_rn(f.y, SCALED ? sc.scale : 1.0f);
+        const uint32_t q = round_pair_fp4(__byte_perm(__float_as_uint(f.x), __float_as_uint(f.y), 0x7632));
+        float2 g = unpack_bf16x2(q);
+        if (SCALED) { g.x *= sc.rscale; g.y *= sc.rscale; }
+        put_pair<DT>(v, k, g);
+      }
+    }
   } else if (FMT == FPEMU_FMT_BF16 && DT == FPEMU_DT_BF16) {
     // a bf16 tensor cast to BFLOAT16: every rounding mode is the identity (stochastic bits are added below the
     // kept bits and never carry); only the flush of exponent-field-0 values to +0 remains

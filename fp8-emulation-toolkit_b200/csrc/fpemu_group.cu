@@ -65,6 +65,134 @@ __global__ void __launch_bounds__(256) group_reg_kernel(const CastArgs a_, const
   }
 }
 
+// Rows whose vector count fits no power-of-two group shape well (576 bf16 columns = 36 vectors: the tightest shape,
+// 16 threads x 3, leaves a quarter of its slots — and of the issue slots of an instruction-bound cast — empty).
+// Here a CTA takes `rows_per_cta` WHOLE consecutive rows, which are one contiguous run of vectors, and deals the
+// vectors to its threads without regard to the row boundaries: thread t holds vectors t, t + T, ... (R of them), so
+// that only the last few slots of the CTA are idle (36 vectors: 14 rows = 504 of 512 slots).  The row maxima are
+// collected in shared memory — per warp and slot one REDUX per distinct row (at most two when a row has 32 vectors or
+// more) and one shared atomicMax by its first lane — the first `rows` threads turn them into scales, and every thread
+// picks up the scale of each of its vectors' rows.
+constexpr int kTileMaxRows = 64;
+
+template <int FMT, int RND, int DT, int R>
+__global__ void __launch_bounds__(256) rows_tile_kernel(const CastArgs a_, const int64_t rows, const int vpg,
+                                                       const int rows_per_cta, const uint32_t inv, const int rule,
+                                                       const float flt_max, float* d_scale_out) {
+  const CastArgs a = with_device_seed(a_);
+  constexpr int VE = DtInfo<DT>::kVecElems;
+  __shared__ uint32_t row_bits[kTileMaxRows];
+  __shared__ float row_scale[kTileMaxRows];
+  const int T = blockDim.x;
+  const int64_t row0 = (int64_t)blockIdx.x * rows_per_cta;
+  const int nrows = (int)((rows - row0) < (int64_t)rows_per_cta ? (rows - row0) : (int64_t)rows_per_cta);
+  const int nv = nrows * vpg;
+  const int64_t v0 = row0 * vpg;
+  const char* in = static_cast<const char*>(a.in);
+  char* out = static_cast<char*>(a.out);
+  if ((int)threadIdx.x < kTileMaxRows) row_bits[threadIdx.x] = 0u;
+  Vec32 v[R];
+#pragma unroll
+  for (int j = 0; j < R; ++j) {
+    const int vi = j * T + threadIdx.x;
+    if (vi < nv) v[j] = ldg256(in + (v0 + vi) * 32);
+    else {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) v[j].w[i] = 0u;
+    }
+  }
+  __syncthreads();
+  const int lane = threadIdx.x & 31;
+#pragma unroll
+  for (int j = 0; j < R; ++j) {
+    const int vi = j * T + threadIdx.x;
+    const bool active = vi < nv;
+    const int r = (int)(((uint32_t)vi * inv) >> 24);                       // vi / vpg (host-checked magic)
+    const uint32_t bits = __float_as_uint(vec_absmax<DT, true>(v[j]));     // a NaN sorts above every number
+    uint32_t todo = __ballot_sync(0xFFFFFFFFu, active);
+    while (todo != 0u) {
+      const int leader = __ffs(todo) - 1;
+      const int rl = __shfl_sync(0xFFFFFFFFu, r, leader);
+      const bool mine = active && r == rl;
+      const uint32_t m = __reduce_max_sync(0xFFFFFFFFu, mine ? bits : 0u);
+      if (lane == leader && m > row_bits[rl]) atomicMax(&row_bits[rl], m);
+      todo &= ~__ballot_sync(0xFFFFFFFFu, mine);
+    }
+  }
+  __syncthreads();
+  if ((int)threadIdx.x < nrows) {
+    const float s_host = scale_from_amax(__uint_as_float(row_bits[threadIdx.x]), flt_max, rule == kRuleRowClamp, DT);
+    if (d_scale_out != nullptr) d_scale_out[row0 + threadIdx.x] = s_host;
+    row_scale[threadIdx.x] = effective_scale(s_host, DT);
+  }
+  __syncthreads();
+  ScaleCtx sc;
+  sc.unscale32 = (a.flags & FPEMU_FLAG_UNSCALE_FP32) != 0;
+#pragma unroll
+  for (int j = 0; j < R; ++j) {
+    const int vi = j * T + threadIdx.x;
+    if (vi < nv) {
+      sc.scale = row_scale[((uint32_t)vi * inv) >> 24];
+      sc.rscale = __frcp_rn(sc.scale);
+      process_vec<FMT, RND, false, DT, true>(v[j], sc, a, a.elem_offset + (uint64_t)(v0 + vi) * VE);
+      stg256(out + (v0 + vi) * 32, v[j]);
+    }
+  }
+}
+
+typedef void (*TileKernel)(const CastArgs, const int64_t, const int, const int, const uint32_t, const int, const float, float*);
+
+template <int FMT, int RND, int DT>
+static TileKernel tile_g(int r) {
+  if (r == 2) return rows_tile_kernel<FMT, RND, DT, 2>;
+  if (r == 3) return rows_tile_kernel<FMT, RND, DT, 3>;
+  return rows_tile_kernel<FMT, RND, DT, 4>;
+}
+template <int FMT, int RND>
+static TileKernel tile_dt(int dt, int r) {
+  switch (dt) {
+    case FPEMU_DT_F32:  return tile_g<FMT, RND, FPEMU_DT_F32>(r);
+    case FPEMU_DT_F16:  return tile_g<FMT, RND, FPEMU_DT_F16>(r);
+    default:            return tile_g<FMT, RND, FPEMU_DT_BF16>(r);
+  }
+}
+template <int FMT>
+static TileKernel tile_rnd(int rnd, int dt, int r) {
+  switch (rnd) {
+    case FPEMU_RND_RNE:        return tile_dt<FMT, FPEMU_RND_RNE>(dt, r);
+    case FPEMU_RND_RTZ:        return tile_dt<FMT, FPEMU_RND_RTZ>(dt, r);
+    case FPEMU_RND_STOCHASTIC: return tile_dt<FMT, FPEMU_RND_STOCHASTIC>(dt, r);
+    default:                   return nullptr;
+  }
+}
+
+// Threads per CTA (a multiple of 32), vectors per thread (2-4) and whole rows per CTA: among the shapes within 2 % of
+// the fewest idle slots, the smallest CTA (then the fewest vectors per thread) — at equal slot use small CTAs measured
+// faster (4608 bf16 columns: 96 x 3 = one row per CTA 6.15 TB/s, 192 x 3 = two rows 5.87 TB/s), the three CTA-wide
+// barriers wait on fewer warps.  Returns the fraction of slots in use (0: rows of this length do not fit).
+static double tile_shape(int64_t vpg, int* threads, int* r, int* rows_per_cta) {
+  if (vpg < 16 || vpg > 256 * 4) return 0.0;
+  double best = 0.0;
+  for (int pass = 0; pass < 2; ++pass) {
+    int64_t best_slots = -1;
+    for (int rr = 2; rr <= 4; ++rr) {
+      for (int t = 64; t <= 256; t += 32) {
+        const int64_t slots = (int64_t)t * rr;
+        if (slots < vpg) continue;
+        int64_t rpc = slots / vpg;
+        if (rpc > kTileMaxRows) rpc = kTileMaxRows;
+        const double eff = (double)(rpc * vpg) / (double)slots;
+        if (pass == 0) {
+          if (eff > best) best = eff;
+        } else if (eff >= best - 0.02 && (best_slots < 0 || slots < best_slots)) {
+          best_slots = slots; *threads = t; *r = rr; *rows_per_cta = (int)rpc;
+        }
+      }
+    }
+  }
+  return best - 0.02 > 0.0 ? (double)((int64_t)*rows_per_cta * vpg) / (double)((int64_t)*threads * *r) : 0.0;
+}
+
 typedef void (*GroupKernel)(const CastArgs, const int64_t, const int, const int, const int, const float, float*);
 
 template <int FMT, int RND, int DT>
@@ -98,6 +226,30 @@ static GroupKernel pick_rnd(int rnd, int dt, int r) {
 bool launch_group_reg(const CastArgs& a, int dtype, int64_t groups, int64_t vectors_per_group, int rule, float flt_max,
                       float* d_scale_out, cudaStream_t stream, int* status) {
   int lg, r;
+  // rows only: the tile kernel when the best power-of-two shape would leave more than a tenth of its slots empty and
+  // the tile shape does better
+  if (rule != kRuleBlockPow2) {
+    int tt = 0, tr = 0, rpc = 0;
+    const double tile_eff = tile_shape(vectors_per_group, &tt, &tr, &rpc);
+    double pow2_eff = 0.0;
+    if (group_shape_tight(vectors_per_group, &lg, &r)) pow2_eff = (double)vectors_per_group / (double)((int64_t)r << lg);
+    if (tile_eff > 0.0 && pow2_eff < 0.9 && tile_eff > pow2_eff + 0.04) {
+      TileKernel tk = nullptr;
+      switch (a.fmt) {
+        case FPEMU_FMT_E5M2: tk = tile_rnd<FPEMU_FMT_E5M2>(a.rnd, dtype, tr); break;
+        case FPEMU_FMT_E4M3: tk = tile_rnd<FPEMU_FMT_E4M3>(a.rnd, dtype, tr); break;
+        case FPEMU_FMT_E3M4: tk = tile_rnd<FPEMU_FMT_E3M4>(a.rnd, dtype, tr); break;
+        default: break;
+      }
+      const int64_t grid = (groups + rpc - 1) / rpc;
+      if (tk != nullptr && grid <= 0x7FFFFFFFLL) {
+        const uint32_t inv = (uint32_t)((1u << 24) / (uint32_t)vectors_per_group) + 1u;   // exact for vi < 1024, vpg >= 16
+        tk<<<(unsigned)grid, tt, 0, stream>>>(a, groups, (int)vectors_per_group, rpc, inv, rule, flt_max, d_scale_out);
+        *status = (int)cudaGetLastError();
+        return true;
+      }
+    }
+  }
   if (!group_shape_tight(vectors_per_group, &lg, &r)) return false;
   GroupKernel k = nullptr;
   switch (a.fmt) {

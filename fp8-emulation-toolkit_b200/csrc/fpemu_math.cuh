@@ -384,6 +384,25 @@ __device__ __forceinline__ float round_one_fp4(float v) {
   return __uint_as_float(sign | (f << 23));
 }
 
+// FP4, two values at a time.  round_one_fp4() looks only at the sign, the exponent and the top two mantissa bits of
+// the fp32 value, all of which sit in the upper 16 bits — the bfloat16 encoding — so two values are rounded as one
+// 32-bit word of two bf16 encodings, and the result (a power of 4, or 0) is again a bf16 encoding, exactly.
+// With n = |b| >> 5 (exponent field f and two mantissa bits) the rule "an even f goes up when the mantissa is >= 1.25,
+// down otherwise; an odd f stays" is f' = 2 * ((n + 7) >> 3) - 1, i.e. (f' << 7) = ((|b| - 0x20) & 0xFF00) | 0x80.
+//   clamp to [-1, 1]    |v| >= 1, Inf -> 1; NaN -> +1 (the reference multiplies by the scale first, which makes every
+//                       NaN the positive canonical one)
+//   bit 14              is 0 after the clamp: set, it keeps the per-lane subtraction from borrowing across lanes
+//   keep                |v| >= 1.25 * 2^-13 (f' >= 115), everything smaller is +0
+__device__ __forceinline__ uint32_t round_pair_fp4(uint32_t b) {
+  uint32_t c;
+  asm("{.reg .b32 t, n; min.bf16x2 t, %1, %2; neg.bf16x2 n, %2; max.bf16x2 %0, t, n;}" : "=r"(c) : "r"(b), "r"(0x3F803F80u));
+  const uint32_t aabs = c & kAbs2;
+  const uint32_t thr = 0x39203920u;
+  const uint32_t keep = __hge2_mask(*reinterpret_cast<const __nv_bfloat162*>(&aabs), *reinterpret_cast<const __nv_bfloat162*>(&thr));
+  const uint32_t t = (c | 0x40004000u) - 0x00200020u;
+  return ((t & 0xBF00BF00u) | 0x00800080u) & keep;
+}
+
 // Full QDQ of one fp32 value (already widened from the tensor's dtype).  `scale`/`rscale` are what the
 // kernel uses (for fp16 tensors the scale has been rounded to half, see cast kernels).
 __device__ __forceinline__ float cast_one(float x, int fmt, int rnd, int flags, bool scaled, float scale,

@@ -21,15 +21,16 @@ __device__ __forceinline__ float vec_absmax(const Vec32& v) {
   } else if (DT == FPEMU_DT_F16) {
     __half2 m = as_h2(0u);
 #pragma unroll
-    for (int i = 0; i < 8; ++i) m = NANPROP ? __hmax2_nan(m, as_h2(v.w[i] & kAbs2)) : __hmax2(m, as_h2(v.w[i] & kAbs2));
+    for (int i = 0; i < 8; ++i) m = NANPROP ? __hmax2_nan(m, __habs2(as_h2(v.w[i]))) : __hmax2(m, __habs2(as_h2(v.w[i])));   // |x| as an operand modifier
     return NANPROP ? absmax_nan(__low2float(m), __high2float(m)) : fmaxf(__low2float(m), __high2float(m));
   } else {
     uint32_t z = 0u;
     __nv_bfloat162 m = *reinterpret_cast<__nv_bfloat162*>(&z);
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-      uint32_t a = v.w[i] & kAbs2;
-      m = NANPROP ? __hmax2_nan(m, *reinterpret_cast<__nv_bfloat162*>(&a)) : __hmax2(m, *reinterpret_cast<__nv_bfloat162*>(&a));
+      uint32_t w = v.w[i];
+      const __nv_bfloat162 a = __habs2(*reinterpret_cast<__nv_bfloat162*>(&w));
+      m = NANPROP ? __hmax2_nan(m, a) : __hmax2(m, a);
     }
     return NANPROP ? absmax_nan(__low2float(m), __high2float(m)) : fmaxf(__low2float(m), __high2float(m));
   }

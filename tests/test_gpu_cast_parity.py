@@ -363,7 +363,8 @@ def test_per_tensor_amax_scaled_cast_without_host_sync(F):
 
 @pytest.mark.parametrize("mode", ["E4M3_RNE", "E3M4_RNE", "E5M2_RNE", "E4M3_STOCHASTIC"])
 @pytest.mark.parametrize("shape", [(64, 147), (128, 576), (7, 4608), (1000, 16), (3, 5), (16, 1280), (4, 12288),
-                                   (3, 12296), (5, 24576), (2, 24592), (9, 1024), (9, 1032)])
+                                   (3, 12296), (5, 24576), (2, 24592), (9, 1024), (9, 1032),
+                                   (45, 592), (130, 272), (67, 1152), (1, 576)])   # whole-rows-per-CTA tile kernel
 @pytest.mark.parametrize("dt", ["f32", "f16"])
 def test_rowwise_per_channel_cast(F, mode, shape, dt):
     rng = np.random.default_rng(shape[0])
