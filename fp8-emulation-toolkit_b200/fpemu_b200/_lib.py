@@ -23,6 +23,7 @@ SIGNATURES = {
     "fpemu_strerror": (_cp, [_i32]),
     "fpemu_parse_mode": (_i32, [_cp, ctypes.POINTER(_i32), ctypes.POINTER(_i32), ctypes.POINTER(_i32)]),
     "fpemu_cast": (_i32, [_vp, _vp, _i64, _i32, _i32, _i32, _i32, _f32, _vp, _u64, _u64, _vp]),
+    "fpemu_cast_f64": (_i32, [_vp, _vp, _i64, _i32, _i32, _i32, _f32, _vp, _u64, _u64, _vp]),
     "fpemu_cast_blocked": (_i32, [_vp, _vp, _i64, _i64, _i32, _i32, _i32, _i32, _u64, _u64, _vp]),
     "fpemu_amax": (_i32, [_vp, _i64, _i32, _vp, _vp]),
     "fpemu_scale_from_amax": (_i32, [_vp, _i32, _f32, _vp, _vp]),

@@ -145,8 +145,12 @@ def cast(x, mode, out=None, scale=1.0, d_scale=None, seed=None, elem_offset=0, n
             raise ValueError("fpemu: d_scale must be a float32 CUDA tensor")
         dptr = d_scale.data_ptr()
     with _on_device(x):
-        st = L.lib().fpemu_cast(x.data_ptr(), out.data_ptr(), n, _dt(x), fmt, rnd, flags, float(scale), dptr,
-                                int(seed or 0), int(elem_offset), _stream(x))
+        if x.dtype == torch.float64:                  # the one entry point that takes doubles (fpemu_kernels.cu:1059)
+            st = L.lib().fpemu_cast_f64(x.data_ptr(), out.data_ptr(), n, fmt, rnd, flags, float(scale), dptr,
+                                        int(seed or 0), int(elem_offset), _stream(x))
+        else:
+            st = L.lib().fpemu_cast(x.data_ptr(), out.data_ptr(), n, _dt(x), fmt, rnd, flags, float(scale), dptr,
+                                    int(seed or 0), int(elem_offset), _stream(x))
     L.check(st, "fpemu_cast(%s)" % mode)
     return out
 

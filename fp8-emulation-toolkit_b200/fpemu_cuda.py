@@ -35,8 +35,16 @@ def forward(input, mode, size, inplace, scale, block_norm, block_size):
         raise RuntimeError("input must be contiguous")
     size = int(size)
     fmt, rnd, flags = L.parse_mode(mode)
+    blocked = bool(block_norm)
+    # block_norm is honoured only by the E5M2 / E4M3 / E4M3_IEEE / E3M4 / FP4 kernels (fpemu_kernels.cu:1058-1364)
+    if fmt in (L.FMT_BF16, L.FMT_FP16) or (flags & L.FLAG_DAZ):
+        blocked = False
+    if blocked and int(block_size) != size and size % int(block_size) != 0:
+        blocked = False                            # reference: silently disabled, :1048-1051
     x = input
-    if input.dtype == torch.float64:               # reference converts double -> float first (:98, :126)
+    if input.dtype == torch.float64 and blocked:
+        # double tensors have their own kernel (fpemu_cast_f64) except in blocked mode, where narrowing first is exact:
+        # the block scale is a power of two, so (float)(x * scale) == (float)x * scale
         x = input.float()
     if inplace and x is input:
         out = x
@@ -45,12 +53,6 @@ def forward(input, mode, size, inplace, scale, block_norm, block_size):
     else:
         out = ops.empty_like_coaligned(x)  # every element is written: no memset pass; a view gets an equally aligned output
     host_scale, d_scale = _scale_args(scale)
-    blocked = bool(block_norm)
-    # block_norm is honoured only by the E5M2 / E4M3 / E4M3_IEEE / E3M4 / FP4 kernels (fpemu_kernels.cu:1058-1364)
-    if fmt in (L.FMT_BF16, L.FMT_FP16) or (flags & L.FLAG_DAZ):
-        blocked = False
-    if blocked and int(block_size) != size and size % int(block_size) != 0:
-        blocked = False                            # reference: silently disabled, :1048-1051
     if blocked:
         ops.cast_blocked(x, mode, int(block_size), out=out, n=size)
     else:

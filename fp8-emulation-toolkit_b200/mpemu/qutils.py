@@ -273,7 +273,8 @@ def quantize_tensor(tensor, qtconfig, qtparams, inplace=False):
     if not tensor.is_cuda:
         raise RuntimeError("fpemu: the B200 build has no CPU path; move the tensor to a CUDA device")
     if tensor.dtype == torch.float64:
-        # the reference kernels convert double to float first (fpemu_kernels.cu:98, :126); so does this
+        # double tensors: the scale arithmetic of the branches below is defined on float tensors here; unscaled casts go
+        # straight to the double kernel through fpemu_device_fn / fpemu_cuda.forward
         q = quantize_tensor(tensor.float(), qtconfig, qtparams, inplace=False).to(torch.float64)
         if inplace:
             tensor.copy_(q)

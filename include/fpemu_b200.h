@@ -123,6 +123,14 @@ FPEMU_API int fpemu_parse_mode(const char* mode, int* format, int* rounding, int
 FPEMU_API int fpemu_cast(const void* in, void* out, int64_t n, int dtype, int format, int rounding, int flags,
                float scale, const float* d_scale, uint64_t seed, uint64_t elem_offset, void* stream);
 
+/* The same cast for float64 tensors (in / out: n doubles, 8-byte aligned; in == out allowed).  The reference
+ * dispatches its kernels for double too (AT_DISPATCH_FLOATING_TYPES_AND_HALF, fpemu_kernels.cu:1059 ...): the element is
+ * narrowed to float — `(float)x`, and for the formats that take a scale `(float)(x * (double)scale)`, both operands
+ * double (`scalar_t scale`, :405, :420) — rounded like a float tensor's element and widened back (:136-148).  Same
+ * random field per element index as fpemu_cast.  Only this entry point takes doubles. */
+FPEMU_API int fpemu_cast_f64(const void* in, void* out, int64_t n, int format, int rounding, int flags, float scale,
+                             const float* d_scale, uint64_t seed, uint64_t elem_offset, void* stream);
+
 /* Blocked cast ("block_norm"): every run of block_size consecutive elements gets its own power-of-two
  * scale derived from its absolute maximum, 2*2^floor(log2 max)/K with K = 16384 (E5M2), 8 (E4M3,
  * E4M3_IEEE), 1 (E3M4); FP4 uses 1/max.  Replaces absmax_block + the per-kernel scale derivation,

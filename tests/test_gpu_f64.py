@@ -1,0 +1,103 @@
+"""float64 tensors (fpemu_cast_f64): the reference dispatches its kernels for double as well
+(cuda/fpemu_kernels.cu:1059 ...) — the element is narrowed to float, for the scaled formats AFTER a double-precision
+multiplication by the scale (:405, :420), rounded like a float element and widened back.  Bit-exact against
+  (a) the oracle applied to the narrowed values (numpy does the double multiply and the narrowing), and
+  (b) the reference's own CUDA kernels run on the same double tensor (oracle/_ref/fpemu_cuda_ref.so), when built."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import fpemu_oracle as O
+from oracle import ref_loader
+
+pytestmark = pytest.mark.gpu
+
+MODES = ["E5M2_RNE", "E5M2_RTZ", "E4M3_RNE", "E4M3_RTZ", "E3M4_RNE", "BFLOAT16_RNE", "FLOAT16_RNE", "E4M3_IEEE_RNE",
+         "FP4_NEAREST", "E5M2_RNAZ"]
+
+
+@pytest.fixture(scope="module")
+def F():
+    import fpemu_b200
+    fpemu_b200._lib.lib()
+    return fpemu_b200
+
+
+def wide64(n, seed):
+    rng = np.random.default_rng(seed)
+    x = rng.standard_normal(n) * np.exp2(rng.integers(-20, 18, n))          # full double mantissas
+    x[:8] = [0.0, -0.0, np.inf, -np.inf, 448.0000000001, 1e-300, -65504.0000001, 3.5e38]
+    return x
+
+
+def expected(x64, mode, scale):
+    """Oracle on the narrowed values: y = unscale(round(float(x * double(scale))))."""
+    O.set_nan_mode(False)
+    takes_scale = not mode.startswith(("BFLOAT16", "FLOAT16"))
+    s = np.float32(scale if takes_scale else 1.0)
+    with np.errstate(over="ignore", invalid="ignore"):
+        x32 = (x64 * np.float64(s)).astype(np.float32) if s != 1.0 else x64.astype(np.float32)
+        q = O.cast(x32, mode, scale=1.0)
+        if s != 1.0:
+            rs = np.float32(1.0 / np.float64(s))
+            y = q * rs
+            if mode != "FP4_NEAREST":
+                y = y.astype(np.float16).astype(np.float32)                 # the reference CUDA op un-scales through fp16
+            q = y
+    return q.astype(np.float64)
+
+
+@pytest.mark.parametrize("mode", MODES)
+def test_double_tensors_vs_oracle(F, mode):
+    for n, seed in ((1 << 16, 1), (1000003, 2), (7, 3), (0, 4)):
+        x = wide64(max(n, 8), seed)[:n]
+        xt = torch.from_numpy(x).cuda()
+        for scale in (1.0, 0.125, 3.7):
+            got = F.cast(xt, mode, scale=scale)
+            assert got.dtype == torch.float64
+            want = expected(x, mode, scale)
+            ok = O.same_bits_or_both_nan(got.cpu().numpy().astype(np.float32), want.astype(np.float32))
+            assert ok.all(), "%s n=%d s=%g: %d mismatches" % (mode, n, scale, (~ok).sum())
+            assert np.array_equal(got.cpu().numpy()[ok & ~np.isnan(want)], want[ok & ~np.isnan(want)])
+
+
+@pytest.mark.parametrize("mode", ["E5M2_RNE", "E4M3_RNE", "E3M4_RNE", "BFLOAT16_RNE", "E5M2_RTZ", "E4M3_IEEE_RNE"])
+def test_double_tensors_vs_reference_cuda_kernels(F, mode):
+    ref = ref_loader.load("fpemu_cuda_ref")
+    if ref is None:
+        pytest.skip("oracle/_ref/fpemu_cuda_ref.so not built")
+    x = wide64(1 << 16, 9)
+    x[2:4] = [1e5, -1e5]                              # keep Inf out: the reference's `scale * Inf` paths agree, NaN payloads need not
+    xt = torch.from_numpy(x).cuda()
+    for scale in (1.0, 3.7, 94.09):
+        if mode.startswith("BFLOAT16") and scale != 1.0:
+            continue
+        want = ref.forward(xt.clone(), mode, xt.numel(), False, scale, False, 1)[0]
+        got = F.cast(xt, mode, scale=scale)
+        assert torch.equal(got.view(torch.int64), want.view(torch.int64)), "%s s=%g" % (mode, scale)
+        import fpemu_cuda
+        again = fpemu_cuda.forward(xt.clone(), mode, xt.numel(), False, scale, False, 1)[0]
+        assert torch.equal(again.view(torch.int64), want.view(torch.int64))
+
+
+def test_double_in_place_views_and_stochastic(F):
+    x = torch.from_numpy(wide64(300007, 5)).cuda()
+    want = F.cast(x, "E4M3_RNE", scale=3.7)
+    y = x.clone()
+    F.cast(y, "E4M3_RNE", out=y, scale=3.7)
+    assert torch.equal(y.view(torch.int64), want.view(torch.int64))
+    v = x[3:]                                          # 8-byte aligned only: element-wise kernel
+    assert torch.equal(F.cast(v, "E4M3_RNE", scale=3.7).view(torch.int64), want[3:].view(torch.int64))
+    # stochastic: values that are floats already give the float tensor's result (same random field per element index),
+    # in one piece or in slabs with any element offset
+    xf = (torch.randn(200003, device="cuda") * 3).float()
+    xd = xf.double()
+    for mode in ("E5M2_STOCHASTIC", "E4M3_STOCHASTIC", "BFLOAT16_STOCHASTIC", "FLOAT16_STOCHASTIC"):
+        a = F.cast(xf, mode, seed=77).double()
+        b = F.cast(xd, mode, seed=77)
+        assert torch.equal(a.view(torch.int64), b.view(torch.int64)), mode
+        cut = 1003
+        c = torch.cat([F.cast(xd[:cut].clone(), mode, seed=77), F.cast(xd[cut:].clone(), mode, seed=77, elem_offset=cut)])
+        assert torch.equal(c.view(torch.int64), b.view(torch.int64)), mode
+    with pytest.raises(ValueError):
+        F.cast(x, "E4M3_RNE", scale=70000.0)
