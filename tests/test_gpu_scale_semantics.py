@@ -191,3 +191,19 @@ def test_nan_rows_and_nan_tensors_of_a_list(F, ref_cuda):
     got = F.cast_blocked(b, "E4M3_RNE", 64)
     want = ref_cuda.forward(b.clone(), "E4M3_RNE", b.numel(), False, 1.0, True, 64)[0]
     assert same(got, want)
+
+
+@pytest.mark.parametrize("mode", ["E4M3_RNE", "E5M2_STOCHASTIC", "E3M4_RTZ"])
+def test_rows_tile_kernel_on_bfloat16_equals_row_by_row_casts(F, mode):
+    """bf16 rows that fit no power-of-two group shape (36, 37, 72 or 288 vectors per row) take the whole-rows-per-CTA tile
+    kernel: same bits and scales as one amax-scaled cast per row (the per-tensor path, pinned above), row counts that
+    leave the last CTA short, a NaN in one row, stochastic rounding keyed by the global element index."""
+    for i, (rows, cols) in enumerate([(45, 592), (130, 576), (7, 4608), (29, 1152), (1, 576)]):
+        x = _data((rows, cols), 400 + i, torch.float32).to(torch.bfloat16)
+        if rows > 3:
+            x[3, 5] = float("nan")
+        got, scales = F.cast_rowwise(x, mode, seed=9, return_scales=True)
+        for r in range(rows):
+            want, s = F.cast_amax_scaled(x[r].contiguous(), mode, seed=9, elem_offset=r * cols, return_scale=True, fused=False)
+            assert same(got[r], want), (mode, rows, cols, r)
+            assert (scales[r].item() == s.item()) or (np.isnan(scales[r].item()) and np.isnan(s.item())), (mode, rows, cols, r)
