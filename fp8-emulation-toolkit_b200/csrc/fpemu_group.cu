@@ -82,20 +82,22 @@ __global__ void __launch_bounds__(256) rows_tile_kernel(const CastArgs a_, const
   const CastArgs a = with_device_seed(a_);
   constexpr int VE = DtInfo<DT>::kVecElems;
   __shared__ uint32_t row_bits[kTileMaxRows];
-  __shared__ float row_scale[kTileMaxRows];
+  __shared__ float2 row_scale[kTileMaxRows];                   // (scale, 1 / scale) per row
   const int T = blockDim.x;
   const int64_t row0 = (int64_t)blockIdx.x * rows_per_cta;
   const int nrows = (int)((rows - row0) < (int64_t)rows_per_cta ? (rows - row0) : (int64_t)rows_per_cta);
   const int nv = nrows * vpg;
   const int64_t v0 = row0 * vpg;
-  const char* in = static_cast<const char*>(a.in);
-  char* out = static_cast<char*>(a.out);
+  const char* in = static_cast<const char*>(a.in) + v0 * 32;
+  char* out = static_cast<char*>(a.out) + v0 * 32;
   if ((int)threadIdx.x < kTileMaxRows) row_bits[threadIdx.x] = 0u;
   Vec32 v[R];
+  int row_of[R];
 #pragma unroll
   for (int j = 0; j < R; ++j) {
     const int vi = j * T + threadIdx.x;
-    if (vi < nv) v[j] = ldg256(in + (v0 + vi) * 32);
+    row_of[j] = (int)(((uint32_t)vi * inv) >> 24);                         // vi / vpg (host-checked magic)
+    if (vi < nv) v[j] = ldg256(in + vi * 32);
     else {
 #pragma unroll
       for (int i = 0; i < 8; ++i) v[j].w[i] = 0u;
@@ -105,9 +107,8 @@ __global__ void __launch_bounds__(256) rows_tile_kernel(const CastArgs a_, const
   const int lane = threadIdx.x & 31;
 #pragma unroll
   for (int j = 0; j < R; ++j) {
-    const int vi = j * T + threadIdx.x;
-    const bool active = vi < nv;
-    const int r = (int)(((uint32_t)vi * inv) >> 24);                       // vi / vpg (host-checked magic)
+    const bool active = j * T + (int)threadIdx.x < nv;
+    const int r = row_of[j];
     const uint32_t bits = __float_as_uint(vec_absmax<DT, true>(v[j]));     // a NaN sorts above every number
     uint32_t todo = __ballot_sync(0xFFFFFFFFu, active);
     while (todo != 0u) {
@@ -123,7 +124,8 @@ __global__ void __launch_bounds__(256) rows_tile_kernel(const CastArgs a_, const
   if ((int)threadIdx.x < nrows) {
     const float s_host = scale_from_amax(__uint_as_float(row_bits[threadIdx.x]), flt_max, rule == kRuleRowClamp, DT);
     if (d_scale_out != nullptr) d_scale_out[row0 + threadIdx.x] = s_host;
-    row_scale[threadIdx.x] = effective_scale(s_host, DT);
+    const float s = effective_scale(s_host, DT);
+    row_scale[threadIdx.x] = make_float2(s, __frcp_rn(s));
   }
   __syncthreads();
   ScaleCtx sc;
@@ -132,10 +134,11 @@ __global__ void __launch_bounds__(256) rows_tile_kernel(const CastArgs a_, const
   for (int j = 0; j < R; ++j) {
     const int vi = j * T + threadIdx.x;
     if (vi < nv) {
-      sc.scale = row_scale[((uint32_t)vi * inv) >> 24];
-      sc.rscale = __frcp_rn(sc.scale);
+      const float2 s2 = row_scale[row_of[j]];
+      sc.scale = s2.x;
+      sc.rscale = s2.y;
       process_vec<FMT, RND, false, DT, true>(v[j], sc, a, a.elem_offset + (uint64_t)(v0 + vi) * VE);
-      stg256(out + (v0 + vi) * 32, v[j]);
+      stg256(out + vi * 32, v[j]);
     }
   }
 }
