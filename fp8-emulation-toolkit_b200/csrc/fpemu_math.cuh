@@ -141,7 +141,7 @@ __device__ __forceinline__ uint32_t clamp_h2(uint32_t h, uint32_t c) {
 //   flush  factor sat(B - p) in {0, 1} with B = 9 (E4M3: keep p <= 8) / 17 (E3M4: keep p <= 16), applied with a
 //          final HMUL2 so the sign of a flushed value survives (HFMA2.SAT + HMUL2, FMA pipe).
 // Everything works on the signed encoding (sign-magnitude: adding to the low bits never reaches bit 15), so no
-// abs / sign-merge is needed.  Per pair: 8 ALU-pipe + 5 FMA-pipe instructions for RNE; the ALU pipe is what
+// abs / sign-merge is needed.  Per pair: 7 ALU-pipe + 5 FMA-pipe instructions for RNE; the ALU pipe is what
 // bounds the 16-bit tensor variants (profiles/).
 template <int FMT, int RND>
 __device__ __forceinline__ uint32_t round_pair_e4m3_like(uint32_t h, uint32_t r2) {
@@ -149,17 +149,21 @@ __device__ __forceinline__ uint32_t round_pair_e4m3_like(uint32_t h, uint32_t r2
   constexpr uint32_t kSat = E4 ? 0x5F005F00u : 0x4F804F80u;
   constexpr uint32_t kKeep = E4 ? 0xFF80FF80u : 0xFFC0FFC0u;
   constexpr uint32_t kHalfM1 = E4 ? 0x003F003Fu : 0x001F001Fu;
-  constexpr uint32_t kGridExp = E4 ? 0x60006000u : 0x70007000u;   // (15 + G) << 10
+  constexpr uint32_t kGridMul = E4 ? 0x20002000u : 0x30003000u;   // 2^(G - 16): 2^-7 / 2^-3
+  constexpr uint32_t kGridNeg = kGridMul | 0x80008000u;
   constexpr uint32_t kKeepBias = E4 ? 0x48804880u : 0x4C404C40u;  // 9.0 / 17.0
   constexpr int kL = E4 ? 7 : 6;
   const uint32_t c = clamp_h2(h, kSat);                           // saturate; NaN and Inf lanes become the maximum
-  const __half2 p = as_h2(kGridExp - (c & 0x7C007C00u));          // 2^(G - e) per lane
-  const __half2 keepf = __hfma2_sat(p, as_h2(0xBC00BC00u), as_h2(kKeepBias));   // 1.0 keep, 0.0 flush
+  // p = 2^(G - e) per lane, never materialised: the inverted exponent field IS the fp16 number x = 2^(16 - E) (one
+  // LOP3; +Inf for a zero / subnormal lane, which makes p infinite and the lane flushed, as it must be), and the
+  // factor 2^(G - 16) rides in the two HFMA2 that consume p
+  const __half2 x = as_h2(~c & 0x7C007C00u);
+  const __half2 keepf = __hfma2_sat(x, as_h2(kGridNeg), as_h2(kKeepBias));      // sat(B - p): 1.0 keep, 0.0 flush
   uint32_t r;
   if (RND == FPEMU_RND_RTZ) {
     r = c & kKeep;                                                // clearing <= 4 low bits first changes nothing
   } else {
-    const __half2 m = __hfma2_relu(p, as_h2(0x3C003C00u), as_h2(0xBC00BC00u));  // 2^d - 1 (0 when d <= 0)
+    const __half2 m = __hfma2_relu(x, as_h2(kGridMul), as_h2(0xBC00BC00u));     // relu(p - 1) = 2^d - 1 (0 when d <= 0)
     const uint32_t q = as_u32(__hadd2(m, as_h2(0x64006400u)));    // 1024 + (2^d - 1): the mask sits in the mantissa
     const uint32_t ac = c & ~(q ^ 0x64006400u);                   // clear the low d bits
     uint32_t inc;
@@ -179,13 +183,13 @@ __device__ __forceinline__ uint32_t round_pair_e4m3_ieee(uint32_t h, uint32_t r2
   const __half2 av = as_h2(h & kAbs2);
   const uint32_t big = ~__hlt2_mask(av, as_h2(0x5C005C00u));                    // >= 256, or NaN
   const uint32_t rounds = __hlt2_mask(av, as_h2(0x4B804B80u));                   // < 15.0
-  const __half2 p = as_h2(0x60006000u - (h & 0x7C007C00u));                     // 2^(9 - e) per lane
-  const __half2 keepf = __hfma2_sat(p, as_h2(0xBC00BC00u), as_h2(0x48804880u)); // 1.0 keep, 0.0 flush (|h| < 2^-9)
+  const __half2 x = as_h2(~h & 0x7C007C00u);                                    // 2^(16 - E); p = 2^(9 - e) = x * 2^-7
+  const __half2 keepf = __hfma2_sat(x, as_h2(0xA000A000u), as_h2(0x48804880u)); // 1.0 keep, 0.0 flush (|h| < 2^-9)
   uint32_t r;
   if (RND == FPEMU_RND_RTZ) {
     r = h & 0xFF80FF80u;
   } else {
-    const __half2 m = __hfma2_relu(p, as_h2(0x3C003C00u), as_h2(0xBC00BC00u));  // 2^d - 1
+    const __half2 m = __hfma2_relu(x, as_h2(0x20002000u), as_h2(0xBC00BC00u));  // 2^d - 1
     const uint32_t q = as_u32(__hadd2(m, as_h2(0x64006400u)));
     const uint32_t ac = h & ~(q ^ 0x64006400u);                                 // clear the low d bits
     uint32_t inc;

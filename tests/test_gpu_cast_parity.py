@@ -410,8 +410,11 @@ def test_errors_are_exceptions_not_exit(F):
         F.cast(torch.ones(16), "E4M3_RNE")
     with pytest.raises(RuntimeError):
         F.cast(torch.ones(4, 4, device="cuda").t(), "E4M3_RNE")
+    assert F.cast(x.double(), "E4M3_RNE").dtype == torch.float64       # doubles have their own entry point (test_gpu_f64.py)
     with pytest.raises(TypeError):
-        F.cast(x.double(), "E4M3_RNE")
+        F.cast(x.to(torch.int32), "E4M3_RNE")
+    with pytest.raises(TypeError):
+        F.cast_amax_scaled(x.double(), "E4M3_RNE")                     # ... and only that one
     with pytest.raises(ValueError):
         F.cast_blocked(x, "E4M3_RNE", 5)
 
