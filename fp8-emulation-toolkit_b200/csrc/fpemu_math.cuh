@@ -141,18 +141,16 @@ __device__ __forceinline__ uint32_t clamp_h2(uint32_t h, uint32_t c) {
 //   flush  factor sat(B - p) in {0, 1} with B = 9 (E4M3: keep p <= 8) / 17 (E3M4: keep p <= 16), applied with a
 //          final HMUL2 so the sign of a flushed value survives (HFMA2.SAT + HMUL2, FMA pipe).
 // Everything works on the signed encoding (sign-magnitude: adding to the low bits never reaches bit 15), so no
-// abs / sign-merge is needed.  Per pair: 7 ALU-pipe + 5 FMA-pipe instructions for RNE; the ALU pipe is what
-// bounds the 16-bit tensor variants (profiles/).
+// abs / sign-merge is needed.  Per pair: 6 ALU-pipe + 7 FMA-pipe instructions for RNE (the rounding itself is two HFMA2:
+// see below); the ALU pipe, which issues every other cycle, is what bounds the 16-bit tensor variants (profiles/).
 template <int FMT, int RND>
 __device__ __forceinline__ uint32_t round_pair_e4m3_like(uint32_t h, uint32_t r2) {
   constexpr bool E4 = (FMT == FPEMU_FMT_E4M3);
   constexpr uint32_t kSat = E4 ? 0x5F005F00u : 0x4F804F80u;
   constexpr uint32_t kKeep = E4 ? 0xFF80FF80u : 0xFFC0FFC0u;
-  constexpr uint32_t kHalfM1 = E4 ? 0x003F003Fu : 0x001F001Fu;
   constexpr uint32_t kGridMul = E4 ? 0x20002000u : 0x30003000u;   // 2^(G - 16): 2^-7 / 2^-3
   constexpr uint32_t kGridNeg = kGridMul | 0x80008000u;
   constexpr uint32_t kKeepBias = E4 ? 0x48804880u : 0x4C404C40u;  // 9.0 / 17.0
-  constexpr int kL = E4 ? 7 : 6;
   const uint32_t c = clamp_h2(h, kSat);                           // saturate; NaN and Inf lanes become the maximum
   // p = 2^(G - e) per lane, never materialised: the inverted exponent field IS the fp16 number x = 2^(16 - E) (one
   // LOP3; +Inf for a zero / subnormal lane, which makes p infinite and the lane flushed, as it must be), and the
@@ -166,10 +164,18 @@ __device__ __forceinline__ uint32_t round_pair_e4m3_like(uint32_t h, uint32_t r2
     const __half2 m = __hfma2_relu(x, as_h2(kGridMul), as_h2(0xBC00BC00u));     // relu(p - 1) = 2^d - 1 (0 when d <= 0)
     const uint32_t q = as_u32(__hadd2(m, as_h2(0x64006400u)));    // 1024 + (2^d - 1): the mask sits in the mantissa
     const uint32_t ac = c & ~(q ^ 0x64006400u);                   // clear the low d bits
-    uint32_t inc;
-    if (RND == FPEMU_RND_RNE) inc = kHalfM1 + (__umulhi(ac, 1u << (32 - kL)) & 0x00010001u);   // + lsb (ties to even)
-    else inc = r2;
-    r = (ac + inc) & kKeep;                                       // a saturated lane has zero low bits: unchanged
+    if (RND == FPEMU_RND_RNE) {
+      // round to nearest even at the kept mantissa position by letting the FMA pipe do it: with M = +-2^(e + 10 - kept
+      // bits) (the lane's own power of two, same sign), ac + M has exactly the wanted ulp and the hardware rounds the
+      // sum to nearest even; subtracting M again is exact.  x - x is +0 whatever the signs, so the sign of a zero lane
+      // is taken from the sum.  A zero / subnormal lane has M = +-0 and passes through (it is flushed below).
+      const __half2 pw = as_h2(c & 0xFC00FC00u);                                 // +-2^e
+      const __half2 t = __hfma2(pw, as_h2(E4 ? 0x58005800u : 0x54005400u), as_h2(ac));          // ac + M
+      const uint32_t d = as_u32(__hfma2(pw, as_h2(E4 ? 0xD800D800u : 0xD400D400u), t));         // (ac + M) - M
+      r = (d & kAbs2) | (as_u32(t) & kSign2);
+    } else {
+      r = (ac + r2) & kKeep;                                      // a saturated lane has zero low bits: unchanged
+    }
   }
   return as_u32(__hmul2(as_h2(r), keepf));
 }
