@@ -180,10 +180,10 @@ class ShardedPlan(object):
 
     def __init__(self, slabs, row_offsets=None, cols=None, outs=None, group=None, pipeline=1, exchange="auto"):
         """exchange: "nccl" (one all-reduce(MAX) between the two launches), "peer" (the maxima pushed over NVLink peer
-        memory behind the amax launch and awaited inside the cast launch, PeerExchange) or "auto": peer from 4 ranks
-        up when symmetric memory works here, else nccl.  Measured on the Llama-7B sweep (bf16): at 2 GPUs the
-        all-reduce costs 20 us of a 2.87 ms sweep and the polling cast kernel 1.7 % more than it saves; at 8 GPUs
-        the collective is 27-66 us of 0.77 ms and the peer exchange wins by 1-3 % (0.743 against 0.769 ms)."""
+        memory behind the amax launch and awaited inside the cast launch, PeerExchange) or "auto": peer when there is
+        more than one rank on NCCL and symmetric memory works here, else nccl.  Measured on the Llama-7B sweep (bf16,
+        both exchanges timed alternately in one run, profiles/bench_r2_n*.json): 2.835 against 2.859 ms at 2 GPUs,
+        1.439 against 1.460 ms at 4, 0.743 against 0.769 ms at 8."""
         n = len(slabs)
         row_offsets = row_offsets or [0] * n
         cols = cols or [(x.shape[-1] if x.dim() > 1 else 1) for x in slabs]
@@ -194,7 +194,7 @@ class ShardedPlan(object):
         world, _ = _world(group)
         if exchange not in ("nccl", "peer", "auto"):
             raise ValueError("exchange must be 'nccl', 'peer' or 'auto'")
-        want_peer = exchange == "peer" or (exchange == "auto" and world >= 4 and self.plan.device.type == "cuda"
+        want_peer = exchange == "peer" or (exchange == "auto" and world >= 2 and self.plan.device.type == "cuda"
                                            and dist.get_backend(group) == "nccl")
         if want_peer and world > 1:
             try:
