@@ -183,7 +183,7 @@ class ShardedPlan(object):
         memory behind the amax launch and awaited inside the cast launch, PeerExchange) or "auto": peer when there is
         more than one rank on NCCL and symmetric memory works here, else nccl.  Measured on the Llama-7B sweep (bf16,
         both exchanges timed alternately in one run, profiles/bench_r2_n*.json): 2.835 against 2.859 ms at 2 GPUs,
-        1.439 against 1.460 ms at 4, 0.743 against 0.769 ms at 8."""
+        1.439 against 1.460 ms at 4, 0.739 against 0.770 ms at 8."""
         n = len(slabs)
         row_offsets = row_offsets or [0] * n
         cols = cols or [(x.shape[-1] if x.dim() > 1 else 1) for x in slabs]
