@@ -178,32 +178,44 @@ __global__ void __launch_bounds__(kThreads) cast_multi_kernel(const void* table,
   sc.unscale32 = (a.flags & FPEMU_FLAG_UNSCALE_FP32) != 0;
   const int64_t local_cta = (int64_t)(blockIdx.x - e.cta_cast);
   const int64_t nvec = a.n / VE;
-  const char* in = static_cast<const char*>(a.in);
-  char* out = static_cast<char*>(a.out);
-  const int64_t base = local_cta * (kThreads * U) + threadIdx.x;
+  const int64_t first = local_cta * (kThreads * U);              // this CTA's first vector of the tensor
+  const int64_t rest = nvec - first;
+  const int left = (int)(rest < (int64_t)(kThreads * U) ? rest : (int64_t)(kThreads * U)) - (int)threadIdx.x;
+  const char* in = static_cast<const char*>(a.in) + (first + threadIdx.x) * 32;
+  char* out = static_cast<char*>(a.out) + (first + threadIdx.x) * 32;
   MtPoll poll;
   if (XCHG) poll = mt_poll_begin(proto, t, count);               // exchange mode is its own kernel instance: the poll's
                                                                  // registers would cost the plain kernel a resident CTA
   Vec32 v[U];
 #pragma unroll
-  for (int j = 0; j < U; ++j) {
-    const int64_t vi = base + j * kThreads;
-    if (vi < nvec) v[j] = ldg256(in + vi * 32);
-  }
+  for (int j = 0; j < U; ++j)
+    if (j * kThreads < left) v[j] = ldg256(in + (size_t)j * kThreads * 32);
   // the scale AFTER the loads have been issued: in exchange mode it may have to wait for words that peers write, and
   // that latency would otherwise sit in front of every short-lived CTA's memory traffic
   if (SCALED) {
-    const float s = effective_scale(XCHG ? mt_scale_of<DT>(proto, mt_poll_finish(proto, poll, t, count), t, local_cta == 0)
-                                         : mt_scale<DT>(proto, d_scales, t, count, local_cta == 0), DT);
-    sc.scale = s;
-    sc.rscale = __frcp_rn(s);
+    if (XCHG) {
+      const float s = effective_scale(mt_scale_of<DT>(proto, mt_poll_finish(proto, poll, t, count), t, local_cta == 0), DT);
+      sc.scale = s;
+      sc.rscale = __frcp_rn(s);
+    } else {
+      // one warp derives the scale and its reciprocal (two correctly rounded divisions: ~35 instructions that the
+      // other seven warps of an issue-bound kernel need not repeat); the barrier sits behind the loads' latency
+      __shared__ float s_scale[2];
+      if (threadIdx.x < 32) {
+        const float s = effective_scale(mt_scale<DT>(proto, d_scales, t, count, local_cta == 0), DT);
+        if (threadIdx.x == 0) { s_scale[0] = s; s_scale[1] = __frcp_rn(s); }
+      }
+      __syncthreads();
+      sc.scale = s_scale[0];
+      sc.rscale = s_scale[1];
+    }
   }
 #pragma unroll
   for (int j = 0; j < U; ++j) {
-    const int64_t vi = base + j * kThreads;
-    if (vi < nvec) {
-      process_vec<FMT, RND, false, DT, SCALED, ANYOFF>(v[j], sc, a, a.elem_offset + (uint64_t)vi * VE);
-      stg256(out + vi * 32, v[j]);
+    if (j * kThreads < left) {
+      process_vec<FMT, RND, false, DT, SCALED, ANYOFF>(v[j], sc, a,
+                                                       a.elem_offset + (uint64_t)(first + threadIdx.x + j * kThreads) * VE);
+      stg256(out + (size_t)j * kThreads * 32, v[j]);
     }
   }
   // ragged tail of this tensor: its last CTA, thread 0, through a zero-padded register vector
