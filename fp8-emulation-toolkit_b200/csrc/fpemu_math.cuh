@@ -84,7 +84,7 @@ template <int RND, bool DAZ>
 __device__ __forceinline__ uint32_t round_pair_e5m2(uint32_t h, uint32_t r2) {
   constexpr uint32_t kKeep = 0xFF00FF00u;
   const __half2 hv = as_h2(h);
-  const __half2 av = as_h2(h & kAbs2);
+  const __half2 av = __habs2(as_h2(h));                     // |h| as an operand modifier of its consumers
   const __half2 min_normal = as_h2(h2c(0x0400));
   if (RND == FPEMU_RND_RTZ && !DAZ) return h & kKeep;
   if (!DAZ) {
@@ -143,7 +143,9 @@ __device__ __forceinline__ uint32_t clamp_h2(uint32_t h, uint32_t c) {
 // Everything works on the signed encoding (sign-magnitude: adding to the low bits never reaches bit 15), so no
 // abs / sign-merge is needed.  Per pair: 6 ALU-pipe + 7 FMA-pipe instructions for RNE (the rounding itself is two HFMA2:
 // see below); the ALU pipe, which issues every other cycle, is what bounds the 16-bit tensor variants (profiles/).
-template <int FMT, int RND>
+// MAG = true (the encode kernels, which take the sign from h itself): the result is the rounded MAGNITUDE, and the clamp
+// is a single min(|h|, max) instead of min + max.
+template <int FMT, int RND, bool MAG = false>
 __device__ __forceinline__ uint32_t round_pair_e4m3_like(uint32_t h, uint32_t r2) {
   constexpr bool E4 = (FMT == FPEMU_FMT_E4M3);
   constexpr uint32_t kSat = E4 ? 0x5F005F00u : 0x4F804F80u;
@@ -151,7 +153,8 @@ __device__ __forceinline__ uint32_t round_pair_e4m3_like(uint32_t h, uint32_t r2
   constexpr uint32_t kGridMul = E4 ? 0x20002000u : 0x30003000u;   // 2^(G - 16): 2^-7 / 2^-3
   constexpr uint32_t kGridNeg = kGridMul | 0x80008000u;
   constexpr uint32_t kKeepBias = E4 ? 0x48804880u : 0x4C404C40u;  // 9.0 / 17.0
-  const uint32_t c = clamp_h2(h, kSat);                           // saturate; NaN and Inf lanes become the maximum
+  // saturate; NaN and Inf lanes become the maximum
+  const uint32_t c = MAG ? as_u32(__hmin2(__habs2(as_h2(h)), as_h2(kSat))) : clamp_h2(h, kSat);
   // p = 2^(G - e) per lane, never materialised: the inverted exponent field IS the fp16 number x = 2^(16 - E) (one
   // LOP3; +Inf for a zero / subnormal lane, which makes p infinite and the lane flushed, as it must be), and the
   // factor 2^(G - 16) rides in the two HFMA2 that consume p
@@ -186,7 +189,7 @@ __device__ __forceinline__ uint32_t round_pair_e4m3_like(uint32_t h, uint32_t r2
 // compute garbage that the final select replaces.
 template <int RND>
 __device__ __forceinline__ uint32_t round_pair_e4m3_ieee(uint32_t h, uint32_t r2) {
-  const __half2 av = as_h2(h & kAbs2);
+  const __half2 av = __habs2(as_h2(h));                     // |h| as an operand modifier of its consumers
   const uint32_t big = ~__hlt2_mask(av, as_h2(0x5C005C00u));                    // >= 256, or NaN
   const uint32_t rounds = __hlt2_mask(av, as_h2(0x4B804B80u));                   // < 15.0
   const __half2 x = as_h2(~h & 0x7C007C00u);                                    // 2^(16 - E); p = 2^(9 - e) = x * 2^-7
@@ -267,6 +270,20 @@ __device__ __forceinline__ uint32_t encode_pair(uint32_t q) {
   const uint32_t mag = __umulhi(r, 1u << (E4 ? 25 : 26));                                        // r >> 7 / 6
   const uint32_t sgn = __umulhi(q, 1u << 24);                                                    // sign -> bit 7
   uint32_t code;                                                                                 // bits 0-6 of mag, rest of sgn
+  asm("lop3.b32 %0, %1, %2, 0x007F007F, 0xE4;" : "=r"(code) : "r"(mag), "r"(sgn));
+  return code;
+}
+
+// The same from a rounded MAGNITUDE pair `qm` (round_pair_e4m3_like<..., MAG = true>) and the pair `h` it came from, whose
+// sign bits are the codes'.
+template <int FMT>
+__device__ __forceinline__ uint32_t encode_pair_mag(uint32_t qm, uint32_t h) {
+  constexpr bool E4 = (FMT == FPEMU_FMT_E4M3);
+  const __half2 t = __hadd2(as_h2(qm), as_h2(E4 ? 0x40004000u : 0x4C004C00u));
+  const uint32_t r = as_u32(__hfma2(t, as_h2(E4 ? 0x1C001C00u : 0x0C000C00u), as_h2(E4 ? 0xA000A000u : 0x9C009C00u)));
+  const uint32_t mag = __umulhi(r, 1u << (E4 ? 25 : 26));
+  const uint32_t sgn = __umulhi(h, 1u << 24);
+  uint32_t code;
   asm("lop3.b32 %0, %1, %2, 0x007F007F, 0xE4;" : "=r"(code) : "r"(mag), "r"(sgn));
   return code;
 }
