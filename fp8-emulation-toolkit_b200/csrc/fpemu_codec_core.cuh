@@ -70,7 +70,7 @@ __device__ __forceinline__ void encode_vec(const Vec32& v, const ScaleCtx& sc, c
   for (int k = 0; k < kPairs; ++k) {
     const uint32_t h = pair_to_h<DT, SCALED>(v, k, sc);
     const uint32_t r2 = kSR ? __byte_perm(rw[k >> 1], 0u, (k & 1) ? 0x4342u : 0x4140u) : 0u;
-    if (FMT == FPEMU_FMT_E4M3 || FMT == FPEMU_FMT_E3M4) e[k] = encode_pair_mag<FMT>(round_pair_e4m3_like<FMT, RND, true>(h, r2), h);
+    if (FMT == FPEMU_FMT_E4M3 || FMT == FPEMU_FMT_E3M4) e[k] = encode_pair_mag<FMT>(round_pair_e4m3_like<FMT, RND, 1>(h, r2), h);
     else e[k] = encode_pair<FMT>(round_pair<FMT, RND, DAZ>(h, r2));
   }
   w[0] = w[1] = w[2] = w[3] = 0u;

@@ -140,12 +140,14 @@ __device__ __forceinline__ uint32_t clamp_h2(uint32_t h, uint32_t c) {
 //   mask   2^d - 1 = relu(p - 1), moved into integer bits by adding 1024 (HFMA2.RELU + HADD2, FMA pipe);
 //   flush  factor sat(B - p) in {0, 1} with B = 9 (E4M3: keep p <= 8) / 17 (E3M4: keep p <= 16), applied with a
 //          final HMUL2 so the sign of a flushed value survives (HFMA2.SAT + HMUL2, FMA pipe).
-// Everything works on the signed encoding (sign-magnitude: adding to the low bits never reaches bit 15), so no
-// abs / sign-merge is needed.  Per pair: 6 ALU-pipe + 7 FMA-pipe instructions for RNE (the rounding itself is two HFMA2:
-// see below); the ALU pipe, which issues every other cycle, is what bounds the 16-bit tensor variants (profiles/).
-// MAG = true (the encode kernels, which take the sign from h itself): the result is the rounded MAGNITUDE, and the clamp
-// is a single min(|h|, max) instead of min + max.
-template <int FMT, int RND, bool MAG = false>
+// The stochastic and truncating casts work on the signed encoding (sign-magnitude: adding to the low bits never reaches
+// bit 15), so they need no abs / sign-merge.  Per pair: 5 ALU-pipe + 7 FMA-pipe instructions for RNE (the rounding itself
+// is two HFMA2: see below); the ALU pipe, which issues every other cycle, is what bounds the 16-bit tensor variants.
+// MAG = 1 (the encode kernels, which take the sign from h itself): the result is the rounded MAGNITUDE, and the clamp is a
+// single min(|h|, max) instead of min + max.  MAG = 2: the same with h's sign put back before the flush (the RNE cast: its
+// bit-select for the sign of zero becomes that merge, so the cheaper clamp is a net saving; the stochastic and truncating
+// casts would pay an extra merge and keep the signed form).
+template <int FMT, int RND, int MAG = 0>
 __device__ __forceinline__ uint32_t round_pair_e4m3_like(uint32_t h, uint32_t r2) {
   constexpr bool E4 = (FMT == FPEMU_FMT_E4M3);
   constexpr uint32_t kSat = E4 ? 0x5F005F00u : 0x4F804F80u;
@@ -175,7 +177,7 @@ __device__ __forceinline__ uint32_t round_pair_e4m3_like(uint32_t h, uint32_t r2
       const __half2 pw = as_h2(c & 0xFC00FC00u);                                 // +-2^e
       const __half2 t = __hfma2(pw, as_h2(E4 ? 0x58005800u : 0x54005400u), as_h2(ac));          // ac + M
       const uint32_t d = as_u32(__hfma2(pw, as_h2(E4 ? 0xD800D800u : 0xD400D400u), t));         // (ac + M) - M
-      r = (d & kAbs2) | (as_u32(t) & kSign2);
+      r = MAG == 1 ? d : MAG == 2 ? (d | (h & kSign2)) : ((d & kAbs2) | (as_u32(t) & kSign2));
     } else {
       r = (ac + r2) & kKeep;                                      // a saturated lane has zero low bits: unchanged
     }
@@ -245,7 +247,7 @@ template <int FMT, int RND, bool DAZ>
 __device__ __forceinline__ uint32_t round_pair(uint32_t h, uint32_t r2) {
   if (FMT == FPEMU_FMT_E5M2) return round_pair_e5m2<RND, DAZ>(h, r2);
   if (FMT == FPEMU_FMT_E4M3_IEEE) return round_pair_e4m3_ieee<RND>(h, r2);
-  return round_pair_e4m3_like<FMT, RND>(h, r2);
+  return round_pair_e4m3_like<FMT, RND, RND == FPEMU_RND_RNE ? 2 : 0>(h, r2);
 }
 
 // ------------------------------------------------------------------------------------------ 8-bit codes
