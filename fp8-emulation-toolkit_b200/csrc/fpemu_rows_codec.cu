@@ -212,6 +212,8 @@ typedef void (*DecRowsKernel)(const CastArgs, const int64_t, const float*);
 
 template <int FMT, int RND, int DT>
 static EncRowsKernel er_shape(int r) {
+  if (r == 2) return encode_rows_kernel<FMT, RND, DT, 2>;
+  if (r == 3) return encode_rows_kernel<FMT, RND, DT, 3>;
   if (r == 4) return encode_rows_kernel<FMT, RND, DT, 4>;
   if (r == 6) return encode_rows_kernel<FMT, RND, DT, 6>;
   return encode_rows_kernel<FMT, RND, DT, 8>;
@@ -284,7 +286,7 @@ extern "C" int fpemu_encode_rowwise(const void* in, void* codes, int64_t rows, i
   const bool rng_ok = (rounding != FPEMU_RND_STOCHASTIC) || ((elem_offset & 15u) == 0 && cols % 16 == 0);
   const int64_t vpr = cols / ve;
   int lg = 0, r = 0;
-  if (aligned && rng_ok && !(flags & FPEMU_FLAG_DAZ) && group_shape(vpr, &lg, &r)) {
+  if (aligned && rng_ok && !(flags & FPEMU_FLAG_DAZ) && group_shape_tight(vpr, &lg, &r)) {   // fewest idle vector slots
     EncRowsKernel k = nullptr;
     switch (format) {
       case FPEMU_FMT_E5M2: k = er_rnd<FPEMU_FMT_E5M2>(rounding, dtype, r); break;
