@@ -17,8 +17,10 @@ Outside the timed headline region the same run measures, under `detail` (device 
   bf16      the same 12-mode sweep on a 2^30-element bfloat16 tensor (4 B/elem);
   inplace   the fp32 sweep in place;
   c5        BASELINE configs[4]: the Llama-7B weight set (291 tensors, 6.74 G elements) row-sharded over the N ranks,
-            per-tensor amax-scaled E4M3_RNE through fpemu_b200.dist.ShardedPlan (two launches per run of tensors + one
-            all-reduce(MAX) per run) — STRONG scaling: total work is fixed, bf16 and fp32.
+            per-tensor amax-scaled E4M3_RNE through fpemu_b200.dist.ShardedPlan — STRONG scaling: total work is fixed,
+            bf16 and fp32.  At N > 1 both exchanges of the maxima are timed alternately and must agree bit for bit: one
+            NCCL all-reduce(MAX) between the amax and the cast launch, and the kernels' own exchange over NVLink peer
+            memory (pushed behind the amax launch, awaited inside the cast launch); the faster one is `ms_per_sweep`.
 
 e2e = the sweep through the host-buffer entry point fpemu_cast_host_multi: one pinned host tensor of 2^28 elements
 in, thirteen pinned host tensors out (12 modes + the amax-scaled cast), copies inside the timed region.
