@@ -96,6 +96,17 @@ def test_argument_errors_return_status_codes_without_a_gpu(L):
     assert lib.fpemu_cast_rowwise(p, p, -1, 4, 0, 1, 1, 0, 448.0, None, 0, 0, None) == L.ERR_ARG
     assert lib.fpemu_cast_host(p, p, 16, 0, 1, 1, 0, 1.0, 0, None, None, 16, None, None, None) == L.ERR_ARG
     assert lib.fpemu_cast_host(p, p, 16, 0, 1, 1, 0, 1.0, 0, p, p, 24, None, None, None) == L.ERR_ARG
+    # doubles (fpemu_cast_f64) and the peer-memory exchange: same status codes, nothing launched
+    assert lib.fpemu_cast_f64(p, p, -1, 1, 1, 0, 1.0, None, 0, 0, None) == L.ERR_ARG
+    assert lib.fpemu_cast_f64(p, p, 4, 9, 1, 0, 1.0, None, 0, 0, None) == L.ERR_MODE
+    assert lib.fpemu_cast_f64(p, p, 4, 1, 1, 0, 70000.0, None, 0, 0, None) == L.ERR_SCALE
+    assert lib.fpemu_cast_f64(p + 4, p, 4, 1, 1, 0, 1.0, None, 0, 0, None) == L.ERR_ALIGN
+    assert lib.fpemu_cast_f64(p, p, 0, 1, 1, 0, 1.0, None, 0, 0, None) == 0
+    assert lib.fpemu_exchange_floats(291, 8) == 4 * 32 * 8 * 291
+    assert lib.fpemu_exchange_floats(0, 8) == L.ERR_ARG and lib.fpemu_exchange_floats(4, 17) == L.ERR_ARG
+    assert lib.fpemu_amax_multi_push(p, p, 4, p, None, 2, 0, 1, None) == L.ERR_ARG          # no peer pointers
+    assert lib.fpemu_cast_multi_xchg(p, p, 4, 1, 1, 0, None, 2, 1, 448.0, None, 0, None) == L.ERR_ARG
+    assert lib.fpemu_cast_multi_xchg(p, p, 4, 1, 1, 0, p, 2, 0, 448.0, None, 0, None) == L.ERR_ARG   # epoch 0 is reserved
     for code in (0, -1, -2, -3, -4, -5, -6, 1, 700):
         assert len(L.strerror(code)) > 0
     with pytest.raises(ValueError):
