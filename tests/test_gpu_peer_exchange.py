@@ -59,6 +59,19 @@ def _worker(rank, world, port, q):
                 assert torch.equal(sa, sb)
                 for x, y in zip(codes_a[:4], codes_b[:4]):
                     assert torch.equal(x, y)
+        # many short sweeps back to back (the ranks drift against each other, the buffer halves alternate every sweep,
+        # nothing synchronises the host in between): every sweep must reproduce the first one's scales and codes
+        want_s, want_c = sb.clone(), [c.clone() for c in codes_b[:4]]
+        for sweep in range(400):
+            _, sk = eb.amax_scaled_encode("E4M3_RNE", seed=5)
+            if sweep % 37 == 0 or sweep == 399:
+                torch.cuda.synchronize()
+                assert torch.equal(sk, want_s), sweep
+                for x, y in zip(codes_b[:4], want_c):
+                    assert torch.equal(x, y), sweep
+                if rank == sweep % world:
+                    torch.cuda._sleep(2000000)             # ~1 ms: push this rank behind its peer
+        torch.cuda.synchronize()
         dist.barrier()
         q.put((rank, "ok"))
     except Exception as e:  # noqa: BLE001
