@@ -130,6 +130,27 @@ def cast(x, mode, scale=1.0, unscale_fp32=False, seed=0, elem_offset=0, rand=Non
     return out
 
 
+def cast_f64(x, mode, scale=1.0, unscale_fp32=False, seed=0, elem_offset=0):
+    """QDQ of a float64 array as the reference's kernels do it when dispatched for double
+    (AT_DISPATCH_FLOATING_TYPES_AND_HALF, cuda/fpemu_kernels.cu:1059 ...): `scalar_t scale = in_scale` is a double
+    there (:405), so `float inval = in[gid] * scale` (:420) multiplies in double and narrows once; formats without a
+    scale narrow the element (`__anyfloat2float_rn`, :93-105).  The float is rounded like a float tensor's element; the
+    result, un-scaled by `float scale_reciprocal = 1.0 / scale` and (CUDA op) passed through half (`__half2anyfloat`,
+    :136-148, :461), is widened back."""
+    x = np.ascontiguousarray(x, dtype=np.float64)
+    fmt, _, _ = parse_mode(mode)
+    takes_scale = fmt not in (FMT["BF16"], FMT["FP16"])
+    s = np.float32(scale if takes_scale else 1.0)
+    with np.errstate(over="ignore", invalid="ignore"):
+        x32 = (x * np.float64(s)).astype(np.float32) if s != 1.0 else x.astype(np.float32)
+        q = cast(x32, mode, scale=1.0, seed=seed, elem_offset=elem_offset)
+        if s != 1.0:
+            q = q * np.float32(1.0 / np.float64(s))
+            if not unscale_fp32 and fmt != FMT["FP4"]:
+                q = q.astype(np.float16).astype(np.float32)
+    return q.astype(np.float64)
+
+
 def encode(x, mode, scale=1.0, seed=0, elem_offset=0, rand=None):
     """The rounding of `cast`, returned as the format's one-byte codes (uint8 array)."""
     x = np.ascontiguousarray(x)

@@ -9,6 +9,7 @@ import torch
 
 from oracle import fpemu_oracle as O
 from oracle import ref_loader
+from f64_cases import adversarial_f64
 
 pytestmark = pytest.mark.gpu
 
@@ -31,20 +32,8 @@ def wide64(n, seed):
 
 
 def expected(x64, mode, scale):
-    """Oracle on the narrowed values: y = unscale(round(float(x * double(scale))))."""
     O.set_nan_mode(False)
-    takes_scale = not mode.startswith(("BFLOAT16", "FLOAT16"))
-    s = np.float32(scale if takes_scale else 1.0)
-    with np.errstate(over="ignore", invalid="ignore"):
-        x32 = (x64 * np.float64(s)).astype(np.float32) if s != 1.0 else x64.astype(np.float32)
-        q = O.cast(x32, mode, scale=1.0)
-        if s != 1.0:
-            rs = np.float32(1.0 / np.float64(s))
-            y = q * rs
-            if mode != "FP4_NEAREST":
-                y = y.astype(np.float16).astype(np.float32)                 # the reference CUDA op un-scales through fp16
-            q = y
-    return q.astype(np.float64)
+    return O.cast_f64(x64, mode, scale=scale)
 
 
 @pytest.mark.parametrize("mode", MODES)
@@ -101,3 +90,22 @@ def test_double_in_place_views_and_stochastic(F):
         assert torch.equal(c.view(torch.int64), b.view(torch.int64)), mode
     with pytest.raises(ValueError):
         F.cast(x, "E4M3_RNE", scale=70000.0)
+
+
+@pytest.mark.parametrize("mode,dropped", [("E5M2_RNE", 8), ("E4M3_RNE", 7), ("E3M4_RNE", 6)])
+def test_double_multiply_semantics_on_adversarial_inputs(F, mode, dropped):
+    """Inputs built so that `(float)(x * (double)scale)` and `(float)x * scale` round to different grid points for a large
+    share of the elements (tests/f64_cases.py): the kernel must follow the double multiply, like the reference's."""
+    scale = 3.7
+    x = adversarial_f64(1 << 16, 7, scale, dropped)
+    xt = torch.from_numpy(x).cuda()
+    got = F.cast(xt, mode, scale=scale)
+    want = expected(x, mode, scale)
+    assert np.array_equal(got.cpu().numpy(), want)
+    narrowed_first = F.cast(xt.float(), mode, scale=scale).double().cpu().numpy()
+    if mode != "E3M4_RNE":
+        assert (narrowed_first != want).mean() > 0.1          # the distinction is real on this input
+    ref = ref_loader.load("fpemu_cuda_ref")
+    if ref is not None:
+        r = ref.forward(xt.clone(), mode, xt.numel(), False, scale, False, 1)[0]
+        assert torch.equal(got.view(torch.int64), r.view(torch.int64))
