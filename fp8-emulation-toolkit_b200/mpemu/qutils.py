@@ -263,6 +263,35 @@ def _supported_dtype(t):
     return t.dtype in (torch.float32, torch.float16, torch.bfloat16)
 
 
+def _quantize_double(tensor, qtconfig, qtparams, mode, inplace):
+    """float64 tensors (rare: the reference dispatches them, cuda/fpemu_kernels.cu:1059).  Unscaled and per-tensor scaled
+    casts run the double kernel (fpemu_cast_f64) with the scale derived exactly as the reference derives it — torch
+    arithmetic in double on the device (`flt_max / vmax` = reciprocal * flt_max, qutils.py:282-285; the mean rule
+    :276-281), narrowed to float where the op's `float scale` argument narrows it — and no host sync.  Per-channel and
+    fine-grained modes cast a float copy (their scales are derived in float there)."""
+    fmt = _L.parse_mode(mode)[0]
+    takes_scale = fmt not in (_L.FMT_BF16, _L.FMT_FP16)
+    if qtconfig.scaling is True or not (qtconfig.per_channel or qtconfig.fine_grained):
+        scale = 1.0
+        if qtconfig.scaling is True and takes_scale and tensor.numel() > 0:
+            flat = tensor.detach().flatten()
+            if qtconfig.scaling_method == "mean":
+                flt_min = qtconfig.get_flt_min()
+                mean = torch.abs(torch.mean(torch.abs(flat)))
+                mean = torch.where(mean > 1e-5, mean, torch.full_like(mean, flt_min))
+                scale = torch.clamp(flt_min / mean, min=1.0)
+            else:
+                scale = qtconfig.get_flt_max() / torch.max(torch.abs(flat))
+                scale = torch.where(scale > 3.275e+04, torch.full_like(scale, 6.55e+04), scale)
+            scale = scale.float().reshape(1)
+        return fpemu_device_fn(tensor, mode, inplace=inplace, scale=scale)
+    q = quantize_tensor(tensor.float(), qtconfig, qtparams, inplace=False).to(torch.float64)
+    if inplace:
+        tensor.copy_(q)
+        return tensor
+    return q
+
+
 def quantize_tensor(tensor, qtconfig, qtparams, inplace=False):
     """Single entry point for quantizing a tensor — reference: mpemu/qutils.py:264-345, same branches:
     per-tensor (max / mean), per-channel over dim 0, fine-grained groups, unscaled."""
@@ -273,13 +302,7 @@ def quantize_tensor(tensor, qtconfig, qtparams, inplace=False):
     if not tensor.is_cuda:
         raise RuntimeError("fpemu: the B200 build has no CPU path; move the tensor to a CUDA device")
     if tensor.dtype == torch.float64:
-        # double tensors: the scale arithmetic of the branches below is defined on float tensors here; unscaled casts go
-        # straight to the double kernel through fpemu_device_fn / fpemu_cuda.forward
-        q = quantize_tensor(tensor.float(), qtconfig, qtparams, inplace=False).to(torch.float64)
-        if inplace:
-            tensor.copy_(q)
-            return tensor
-        return q
+        return _quantize_double(tensor, qtconfig, qtparams, mode, inplace)
     fmt = _L.parse_mode(mode)[0]
     takes_scale = fmt not in (_L.FMT_BF16, _L.FMT_FP16)
     flt_max = qtconfig.get_flt_max()

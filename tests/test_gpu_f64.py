@@ -109,3 +109,32 @@ def test_double_multiply_semantics_on_adversarial_inputs(F, mode, dropped):
     if ref is not None:
         r = ref.forward(xt.clone(), mode, xt.numel(), False, scale, False, 1)[0]
         assert torch.equal(got.view(torch.int64), r.view(torch.int64))
+
+
+def test_quantize_tensor_on_double_tensors_equals_the_reference_branch(F):
+    """`mpemu.qutils.quantize_tensor` on float64 tensors: the per-tensor `max` branch (qutils.py:282-287) restated over the
+    reference's own CUDA op — torch derives `flt_max / vmax` in double on the device, the op's `float scale` argument
+    narrows it — and the unscaled cast; bit for bit.  Per-channel modes go through a float copy and stay finite."""
+    ref = ref_loader.load("fpemu_cuda_ref")
+    if ref is None:
+        pytest.skip("oracle/_ref/fpemu_cuda_ref.so not built")
+    from mpemu.qutils import TensorQuantConfig, quantize_tensor
+    g = torch.Generator(device="cuda").manual_seed(3)
+    for i, shape in enumerate([(4, 16, 8, 8), (70001,), (24, 16, 3, 3)]):
+        x = torch.randn(shape, device="cuda", dtype=torch.float64, generator=g) * (3.0 ** (i - 1))
+        for dt, mode, flt_max in (("e4m3", "E4M3_RNE", 448.0), ("e5m2", "E5M2_RNE", 57344.0), ("e3m4", "E3M4_RNE", 30.0)):
+            vmax = torch.max(abs(torch.flatten(x.detach())))
+            scale = flt_max / vmax
+            scale = 6.55e+04 if scale > 3.275e+04 else scale
+            want = ref.forward(x.contiguous(), mode, x.nelement(), False, scale, False, 1)[0]
+            got = quantize_tensor(x, TensorQuantConfig(dt, "rne", "per-tensor"), None)
+            assert got.dtype == torch.float64 and torch.equal(got.view(torch.int64), want.view(torch.int64)), (shape, mode)
+            plain = quantize_tensor(x, TensorQuantConfig(dt, "rne"), None)
+            want_plain = ref.forward(x.contiguous(), mode, x.nelement(), False, 1.0, False, 1)[0]
+            assert torch.equal(plain.view(torch.int64), want_plain.view(torch.int64)), (shape, mode)
+        y = x.clone()
+        out = quantize_tensor(y, TensorQuantConfig("e4m3", "rne", "per-tensor"), None, inplace=True)
+        assert out.data_ptr() == y.data_ptr() and not torch.equal(y, x)
+    w = torch.randn(24, 16, 3, 3, device="cuda", dtype=torch.float64, generator=g)
+    q = quantize_tensor(w, TensorQuantConfig("e4m3", "rne", "per-channel"), None)
+    assert q.dtype == torch.float64 and torch.isfinite(q).all()
